@@ -1,0 +1,111 @@
+#!/usr/bin/env python
+"""Extract the reference's golden HDF5 outputs into small fixtures (tests/golden/*.npz).
+
+Run in the build container, where /root/reference exists:
+
+    python tests/golden/make_golden.py
+
+The GPU box has no /root/reference, so tests read only the committed .npz files.  The source
+files are DLBC's own regression data, tests/runnable/tests/**/reference-data/*.h5 (dataset
+/OutArray), read with dlbc_b200/h5lite.py.  Values are stored bit-exactly (see codec.py).
+"""
+import glob
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+sys.path.insert(0, HERE)
+
+import codec  # noqa: E402
+from dlbc_b200.h5lite import read_dataset  # noqa: E402
+
+T = "/root/reference/tests/runnable/tests/"
+
+
+def g(pattern):
+    files = glob.glob(T + pattern)
+    assert len(files) == 1, (pattern, files)
+    return read_dataset(files[0])
+
+
+def main():
+    # --- lb/merging-droplets-3d (BASELINE config 1): densities + colour at t = 0, 10, 1000
+    out = {}
+    for t in (0, 10, 1000):
+        for name in ("density-red", "density-blue", "colour-red-blue"):
+            a = g(f"lb/merging-droplets-3d/reference-data/{name}-*t{t:08d}.h5")
+            out[f"{name}-t{t}"] = a
+        # colour is exactly red - blue in the reference's files: keep only the densities
+        assert np.array_equal(out[f"colour-red-blue-t{t}"], out[f"density-red-t{t}"] - out[f"density-blue-t{t}"])
+        del out[f"colour-red-blue-t{t}"]
+    codec.save(os.path.join(HERE, "merging-droplets-3d.npz"), **out)
+
+    # --- lb/bdist2-sc-3d: full populations.  The system is lamellae along z, uniform in x and y;
+    # check that on the golden data and keep one z-column [0, 0, :, :].
+    out = {}
+    for t in (0, 10, 100):
+        for c in ("red", "blue"):
+            p = g(f"lb/bdist2-sc-3d/reference-data/population-{c}-*t{t:08d}.h5")
+            assert np.array_equal(p, np.broadcast_to(p[0:1, 0:1], p.shape)), "not uniform in x,y"
+            out[f"population-{c}-t{t}"] = p[0, 0]
+            d = g(f"lb/bdist2-sc-3d/reference-data/density-{c}-*t{t:08d}.h5")
+            assert np.array_equal(d, np.broadcast_to(d[0:1, 0:1], d.shape))
+            out[f"density-{c}-t{t}"] = d[0, 0]
+        col = g(f"lb/bdist2-sc-3d/reference-data/colour-red-blue-*t{t:08d}.h5")
+        out[f"colour-red-blue-t{t}"] = col[0, 0]
+    codec.save(os.path.join(HERE, "bdist2-sc-3d.npz"), **out)
+
+    # --- lb/bdist2-3d: 4^3, no Shan-Chen
+    out = {}
+    for t in (0, 10):
+        for c in ("red", "blue"):
+            out[f"population-{c}-t{t}"] = g(f"lb/bdist2-3d/reference-data/population-{c}-*t{t:08d}.h5")
+            out[f"density-{c}-t{t}"] = g(f"lb/bdist2-3d/reference-data/density-{c}-*t{t:08d}.h5")
+    codec.save(os.path.join(HERE, "bdist2-3d.npz"), **out)
+
+    # --- technical/checkpoint-3d: restart KAT (checkpoint populations + mask -> 5 steps)
+    out = {}
+    R = "technical/checkpoint-3d/reference-data/"
+    for c, name in enumerate(("red", "blue")):
+        out[f"cp-fluids{c}-t0"] = g(R + f"cp/cp-fluids{c}-checkpoint-3d-t00000000.h5")
+        out[f"cp-fluids{c}-t5"] = g(R + f"cp/cp-fluids{c}-checkpoint-3d-t00000005.h5")
+        for t in (0, 5):
+            out[f"population-{name}-t{t}"] = g(R + f"population-{name}-checkpoint-3d-t{t:08d}.h5")
+            out[f"density-{name}-t{t}"] = g(R + f"density-{name}-checkpoint-3d-t{t:08d}.h5")
+    for t in (0, 5):
+        out[f"cp-mask-t{t}"] = g(R + f"cp/cp-mask-checkpoint-3d-t{t:08d}.h5")
+        out[f"colour-red-blue-t{t}"] = g(R + f"colour-red-blue-checkpoint-3d-t{t:08d}.h5")
+    codec.save(os.path.join(HERE, "checkpoint-3d.npz"), **out)
+
+    # --- lb/laplace-droplet-3d: SphereFrac init; t = 0, 10, 100 densities
+    out = {}
+    for t in (0, 10, 100):
+        for c in ("red", "blue"):
+            out[f"density-{c}-t{t}"] = g(f"lb/laplace-droplet-3d/reference-data/density-{c}-*t{t:08d}.h5")
+    codec.save(os.path.join(HERE, "laplace-droplet-3d.npz"), **out)
+
+    # --- lb/poiseuille-2d (D2Q9): bounce-back, SecondOrder, globalAcc, velocity/force dumps
+    out = {}
+    for t in (0, 1000, 100000):
+        out[f"mask-t{t}"] = g(f"lb/poiseuille-2d/reference-data/mask-*t{t:08d}.h5")
+        for c in ("red", "blue"):
+            for f in ("density", "velocity", "force"):
+                out[f"{f}-{c}-t{t}"] = g(f"lb/poiseuille-2d/reference-data/{f}-{c}-*t{t:08d}.h5")
+    codec.save(os.path.join(HERE, "poiseuille-2d.npz"), **out)
+
+    # --- lb/init-2d: the random initialisers (np = 4, nc = [2, 2]) pin Mt19937 + uniform
+    out = {}
+    for name in ("eqdistperturb", "eqdistperturbfrac", "eqdistrandom", "constrandom"):
+        for c in ("red", "blue"):
+            out[f"{name}-{c}"] = g(f"lb/init-2d/reference-data/population-{c}-fluid-init-{name}-2d-t00000000.h5")
+    codec.save(os.path.join(HERE, "init-2d-random.npz"), **out)
+
+    for f in sorted(glob.glob(os.path.join(HERE, "*.npz"))):
+        print(f"{os.path.getsize(f):9d}  {os.path.basename(f)}")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,31 @@
+"""Shared helpers for the parity tests."""
+import numpy as np
+
+# |a-b| <= 1e-12 * max(|b|, s), s = max-abs of the golden field
+RTOL = 1e-12
+
+
+def assert_close(a, b, rtol=RTOL, what=""):
+    a, b = np.asarray(a), np.asarray(b)
+    assert a.shape == b.shape, (what, a.shape, b.shape)
+    s = float(np.max(np.abs(b))) if b.size else 0.0
+    bound = rtol * np.maximum(np.abs(b), s)
+    err = np.abs(a - b)
+    bad = err > bound
+    assert not bad.any(), (
+        f"{what}: {int(bad.sum())} of {bad.size} values outside {rtol:g} relative; "
+        f"max abs err {float(err.max()):.3e} (field scale {s:.3e})")
+
+
+def assert_bitexact(a, b, what=""):
+    a, b = np.asarray(a), np.asarray(b)
+    assert a.shape == b.shape and a.dtype == b.dtype, (what, a.shape, b.shape, a.dtype, b.dtype)
+    if a.dtype.kind == "f":
+        same = a.view(np.uint64) == b.view(np.uint64)
+    else:
+        same = a == b
+    assert same.all(), f"{what}: {int((~same).sum())} of {same.size} values differ bitwise"
+
+
+SC = dict(tau=[1.0, 1.0], gcc=[[0.0, 3.6], [3.6, 0.0]], psi_form="Exponential",
+          eqdist_form="BDist2", enable_shan_chen=True)
