@@ -1,0 +1,53 @@
+// context.h -- the library's per-context state (host side).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/dlbc_cuda.h"
+#include "kernels.h"
+
+struct ncclComm;
+
+struct dlbc_cuda_ctx {
+  dlbc_cuda_config cfg{};
+  dlbc::Geom g{};
+  dlbc::StepParams p{};
+  int device = 0;
+  int variant = DLBC_KERNEL_TWO_PASS;
+
+  cudaStream_t compute = nullptr;  // step kernels
+  cudaStream_t comm = nullptr;     // ghost-plane exchange (NCCL)
+  cudaStream_t copy = nullptr;     // host <-> device staging
+
+  double *f[2] = {nullptr, nullptr};  // populations, A/B: [C][19][sites_g]
+  int cur = 0;                        // f[cur] holds the current state
+  double *psi = nullptr;              // [C][sites_g]
+  double *rho_wall = nullptr;         // [C][sites_g], lazily built when gwc != 0 and solids exist
+  uint8_t *mask = nullptr;            // [sites_g]
+  bool has_solid = false;
+  bool rho_wall_valid = false;
+  bool ghosts_valid = false;          // f[cur] ghost planes hold the neighbours' boundary planes
+  bool force_valid = false;           // f[1-cur] / psi hold the inputs of the last step
+
+  // staging for uploads/downloads/outputs
+  void *stage = nullptr;              // device, stage_bytes
+  size_t stage_bytes = 0;
+  double *partial = nullptr;          // device, reduction partials
+  int *flags = nullptr;               // device, [2]: bad mask value seen, solid count
+  int64_t xchunk = 16;                // x-layers per staged population chunk
+
+  // multi-rank
+  ncclComm *nccl = nullptr;
+  int up = 0, down = 0;               // neighbour ranks in +z / -z
+
+  // events for measurement
+  cudaEvent_t ev_a = nullptr, ev_b = nullptr;
+  std::vector<cudaEvent_t> ev_pool;
+
+  int64_t timestep = 0;
+  int64_t launches = 0;
+  int64_t device_bytes = 0;
+  std::string err;
+};

@@ -1,0 +1,272 @@
+// field_io.cu -- layout conversion between the reference's host arrays (AoS f[x][y][z][q], z
+// fastest, src/dlbc/fields/field.d:114-125) and the device's SoA f[q][zg][y][x] (x fastest),
+// derived output fields (lb/io.d:56-101) and global reductions (density.d:136-180,
+// momentum.d:129-180).  None of this is on the per-step hot path.
+#include "field_io.h"
+
+namespace dlbc {
+
+constexpr int TILE = 16;
+
+// ---- populations: dense AoS chunk [xc][ny][nz][19]  <->  SoA [q][zg][y][x0 + xi] ------------
+// One block per (z-tile, y, x-tile): reads are contiguous runs of TILE*19 doubles per x-layer,
+// writes are contiguous runs of TILE doubles along x; the transposition goes through shared
+// memory (row pitch TILE*19+1 doubles: odd, so the strided phase is bank-conflict free).
+__global__ void __launch_bounds__(256) aos_to_soa_kernel(Geom g, const double *__restrict__ aos, int xc, int x0,
+                                                         double *__restrict__ soa_a, double *__restrict__ soa_b) {
+  __shared__ double tile[TILE][TILE * Q + 1];
+  const int z0 = blockIdx.x * TILE, y = blockIdx.y, xi0 = blockIdx.z * TILE;
+  const int nzt = min(TILE, g.nz - z0), nxt = min(TILE, xc - xi0);
+  const int run = nzt * Q;
+  for (int xi = 0; xi < nxt; xi++) {
+    const double *src = aos + (((int64_t)(xi0 + xi) * g.ny + y) * g.nz + z0) * Q;
+    for (int i = threadIdx.x; i < run; i += blockDim.x) tile[xi][i] = src[i];
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < run * TILE; i += blockDim.x) {
+    const int xi = i % TILE, zq = i / TILE;
+    if (xi >= nxt) continue;
+    const int zz = zq / Q, q = zq % Q;
+    const int64_t dst = (int64_t)q * g.sites_g + ((int64_t)(z0 + zz + 1) * g.ny + y) * g.nx + x0 + xi0 + xi;
+    const double v = tile[xi][zz * Q + q];
+    soa_a[dst] = v;
+    if (soa_b) soa_b[dst] = v;
+  }
+}
+
+__global__ void __launch_bounds__(256) soa_to_aos_kernel(Geom g, const double *__restrict__ soa, int xc, int x0,
+                                                         double *__restrict__ aos) {
+  __shared__ double tile[TILE][TILE * Q + 1];
+  const int z0 = blockIdx.x * TILE, y = blockIdx.y, xi0 = blockIdx.z * TILE;
+  const int nzt = min(TILE, g.nz - z0), nxt = min(TILE, xc - xi0);
+  const int run = nzt * Q;
+  for (int i = threadIdx.x; i < run * TILE; i += blockDim.x) {
+    const int xi = i % TILE, zq = i / TILE;
+    if (xi >= nxt) continue;
+    const int zz = zq / Q, q = zq % Q;
+    tile[xi][zz * Q + q] = soa[(int64_t)q * g.sites_g + ((int64_t)(z0 + zz + 1) * g.ny + y) * g.nx + x0 + xi0 + xi];
+  }
+  __syncthreads();
+  for (int xi = 0; xi < nxt; xi++) {
+    double *dst = aos + (((int64_t)(xi0 + xi) * g.ny + y) * g.nz + z0) * Q;
+    for (int i = threadIdx.x; i < run; i += blockDim.x) dst[i] = tile[xi][i];
+  }
+}
+
+cudaError_t launch_aos_to_soa(const Geom &g, const double *aos, int xc, int x0, double *soa_a, double *soa_b,
+                              cudaStream_t s) {
+  dim3 grid((g.nz + TILE - 1) / TILE, g.ny, (xc + TILE - 1) / TILE);
+  aos_to_soa_kernel<<<grid, 256, 0, s>>>(g, aos, xc, x0, soa_a, soa_b);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_soa_to_aos(const Geom &g, const double *soa, int xc, int x0, double *aos, cudaStream_t s) {
+  dim3 grid((g.nz + TILE - 1) / TILE, g.ny, (xc + TILE - 1) / TILE);
+  soa_to_aos_kernel<<<grid, 256, 0, s>>>(g, soa, xc, x0, aos);
+  return cudaGetLastError();
+}
+
+// ---- mask: dense int32 [nx][ny][nz] <-> uint8 [zg][y][x] ------------------------------------
+// flags[0] |= 1 when a value other than 0/1 is seen (enum Mask, mask.d:84-93); flags[1] counts
+// solid sites (countSites, mask.d:105-116).
+__global__ void mask_in_kernel(Geom g, const int32_t *__restrict__ in, uint8_t *__restrict__ out, int *flags) {
+  __shared__ int32_t tile[32][33];
+  const int x0 = blockIdx.x * 32, y = blockIdx.y, z0 = blockIdx.z * 32;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {  // j: x within tile, threadIdx.x: z
+    const int x = x0 + j, z = z0 + threadIdx.x;
+    if (x < g.nx && z < g.nz) tile[j][threadIdx.x] = in[((int64_t)x * g.ny + y) * g.nz + z];
+  }
+  __syncthreads();
+  int solid = 0;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {  // j: z within tile, threadIdx.x: x
+    const int x = x0 + threadIdx.x, z = z0 + j;
+    if (x < g.nx && z < g.nz) {
+      const int32_t v = tile[threadIdx.x][j];
+      if (v != 0 && v != 1) atomicOr(&flags[0], 1);
+      solid += (v == 1);
+      out[((int64_t)(z + 1) * g.ny + y) * g.nx + x] = (uint8_t)(v == 1);
+    }
+  }
+  if (solid) atomicAdd(&flags[1], solid);
+}
+
+__global__ void mask_out_kernel(Geom g, const uint8_t *__restrict__ in, int32_t *__restrict__ out) {
+  __shared__ int32_t tile[32][33];
+  const int x0 = blockIdx.x * 32, y = blockIdx.y, z0 = blockIdx.z * 32;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int x = x0 + threadIdx.x, z = z0 + j;
+    if (x < g.nx && z < g.nz) tile[j][threadIdx.x] = in[((int64_t)(z + 1) * g.ny + y) * g.nx + x];
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int x = x0 + j, z = z0 + threadIdx.x;
+    if (x < g.nx && z < g.nz) out[((int64_t)x * g.ny + y) * g.nz + z] = tile[threadIdx.x][j];
+  }
+}
+
+cudaError_t launch_mask_in(const Geom &g, const int32_t *in, uint8_t *out, int *flags, cudaStream_t s) {
+  dim3 grid((g.nx + 31) / 32, g.ny, (g.nz + 31) / 32);
+  mask_in_kernel<<<grid, dim3(32, 8), 0, s>>>(g, in, out, flags);
+  return cudaGetLastError();
+}
+cudaError_t launch_mask_out(const Geom &g, const uint8_t *in, int32_t *out, cudaStream_t s) {
+  dim3 grid((g.nx + 31) / 32, g.ny, (g.nz + 31) / 32);
+  mask_out_kernel<<<grid, dim3(32, 8), 0, s>>>(g, in, out);
+  return cudaGetLastError();
+}
+
+// ---- ghost planes when the slab is its own z neighbour ---------------------------------------
+// Populations: only the five directions that cross each face are ever read from a ghost plane
+// (pull of q with c_z = +1 reads zg - 1; c_z = -1 reads zg + 1).  We copy all 19 for simplicity
+// here (setup path); the step kernels maintain just the five during time stepping.
+__global__ void ghost_fill_kernel(Geom g, double *__restrict__ f, int narrays) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.plane) return;
+  for (int a = blockIdx.y; a < narrays; a += gridDim.y) {
+    double *p = f + (int64_t)a * g.sites_g;
+    p[i] = p[(int64_t)g.nz * g.plane + i];                           // ghost 0      <- plane nz
+    p[(int64_t)(g.nz + 1) * g.plane + i] = p[g.plane + i];           // ghost nz + 1 <- plane 1
+  }
+}
+__global__ void ghost_fill_mask_kernel(Geom g, uint8_t *__restrict__ m) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.plane) return;
+  m[i] = m[(int64_t)g.nz * g.plane + i];
+  m[(int64_t)(g.nz + 1) * g.plane + i] = m[g.plane + i];
+}
+cudaError_t launch_ghost_fill(const Geom &g, double *f, int narrays, cudaStream_t s) {
+  dim3 grid((unsigned)((g.plane + 255) / 256), (unsigned)min(narrays, 65535));
+  ghost_fill_kernel<<<grid, 256, 0, s>>>(g, f, narrays);
+  return cudaGetLastError();
+}
+cudaError_t launch_ghost_fill_mask(const Geom &g, uint8_t *m, cudaStream_t s) {
+  ghost_fill_mask_kernel<<<(unsigned)((g.plane + 255) / 256), 256, 0, s>>>(g, m);
+  return cudaGetLastError();
+}
+
+// ---- derived outputs -------------------------------------------------------------------------
+// kind 0: density of comp c1 (densityField, density.d:89-96: every site, solid included)
+// kind 1: colour c1 - c2 (colourField, density.d:284-295: zero on solid sites)
+// kind 2: raw velocity of c1 (rawVelocityField, velocity.d:106-117: zero on solid sites)
+// kind 3: own-site density into an SoA array (no transposition) for rho_wall
+// Output (kinds 0-2): dense [nx][ny][nz][K] (K = 1 or 3), written through a 32x32 (x,z) tile.
+__device__ __forceinline__ void load_site(const double *__restrict__ fc, int64_t qstride, int64_t s, double (&f)[Q]) {
+#pragma unroll
+  for (int q = 0; q < Q; q++) f[q] = fc[(int64_t)q * qstride + s];
+}
+
+template <int KIND>
+__global__ void output_kernel(Geom g, const double *__restrict__ f, const uint8_t *__restrict__ mask, int c1, int c2,
+                              double *__restrict__ out) {
+  constexpr int K = KIND == 2 ? 3 : 1;
+  __shared__ double tile[K][32][33];
+  const int x0 = blockIdx.x * 32, y = blockIdx.y, z0 = blockIdx.z * 32;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {  // j: z in tile; threadIdx.x: x
+    const int x = x0 + threadIdx.x, z = z0 + j;
+    if (x >= g.nx || z >= g.nz) continue;
+    const int64_t s = ((int64_t)(z + 1) * g.ny + y) * g.nx + x;
+    const bool fluid = mask[s] == 0;
+    double fa[Q];
+    load_site(f + (int64_t)c1 * Q * g.sites_g, g.sites_g, s, fa);
+    if (KIND == 0) {
+      tile[0][j][threadIdx.x] = density19(fa);
+    } else if (KIND == 1) {
+      double fb[Q];
+      load_site(f + (int64_t)c2 * Q * g.sites_g, g.sites_g, s, fb);
+      tile[0][j][threadIdx.x] = fluid ? density19(fa) - density19(fb) : 0.0;
+    } else {
+      double m[3];
+      momentum19(fa, m);
+      const double rho = density19(fa);
+#pragma unroll
+      for (int d = 0; d < 3; d++) tile[d][j][threadIdx.x] = fluid ? m[d] / rho : 0.0;
+    }
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {  // j: x in tile; threadIdx.x: z
+    const int x = x0 + j, z = z0 + threadIdx.x;
+    if (x >= g.nx || z >= g.nz) continue;
+    const int64_t o = (((int64_t)x * g.ny + y) * g.nz + z) * K;
+#pragma unroll
+    for (int d = 0; d < K; d++) out[o + d] = tile[d][threadIdx.x][j];
+  }
+}
+
+cudaError_t launch_output(const Geom &g, int kind, const double *f, const uint8_t *mask, int c1, int c2, double *out,
+                          cudaStream_t s) {
+  dim3 grid((g.nx + 31) / 32, g.ny, (g.nz + 31) / 32), block(32, 8);
+  if (kind == 0) output_kernel<0><<<grid, block, 0, s>>>(g, f, mask, c1, c2, out);
+  else if (kind == 1) output_kernel<1><<<grid, block, 0, s>>>(g, f, mask, c1, c2, out);
+  else if (kind == 2) output_kernel<2><<<grid, block, 0, s>>>(g, f, mask, c1, c2, out);
+  else return cudaErrorInvalidValue;
+  return cudaGetLastError();
+}
+
+// Own-site densities of every site incl. ghosts, SoA (for the wall term, force.d:298: the density
+// "on the wall" is the sum of the solid site's own, never-advected populations).
+__global__ void site_density_kernel(Geom g, const double *__restrict__ fc, double *__restrict__ rho) {
+  const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= g.sites_g) return;
+  double f[Q];
+  load_site(fc, g.sites_g, s, f);
+  rho[s] = density19(f);
+}
+cudaError_t launch_site_density(const Geom &g, const double *fc, double *rho, cudaStream_t s) {
+  site_density_kernel<<<(unsigned)((g.sites_g + 255) / 256), 256, 0, s>>>(g, fc, rho);
+  return cudaGetLastError();
+}
+
+// ---- reductions: mass (1 value) and momentum (3 values) over physical fluid sites ---------------
+// Deterministic: fixed grid, each block reduces a fixed range in a fixed tree order, then one
+// block reduces the partials.  partial layout: [4][REDUCE_BLOCKS].
+__device__ __forceinline__ double block_sum(double v, double *sh) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) sh[w] = v;
+  __syncthreads();
+  double r = 0.0;
+  if (w == 0) {
+    r = l < (int)(blockDim.x >> 5) ? sh[l] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) r += __shfl_down_sync(0xffffffffu, r, o);
+  }
+  __syncthreads();
+  return r;
+}
+
+__global__ void __launch_bounds__(256) reduce_sites_kernel(Geom g, const double *__restrict__ fc,
+                                                           const uint8_t *__restrict__ mask, double *__restrict__ partial) {
+  __shared__ double sh[8];
+  double acc[4] = {0.0, 0.0, 0.0, 0.0};
+  const int64_t n = (int64_t)g.nz * g.plane;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t s = i + g.plane;  // skip ghost plane 0
+    if (mask[s]) continue;          // isFluid only (density.d:142, momentum.d:135)
+    double f[Q], m[3];
+    load_site(fc, g.sites_g, s, f);
+    momentum19(f, m);
+    acc[0] += density19(f);
+    acc[1] += m[0]; acc[2] += m[1]; acc[3] += m[2];
+  }
+  for (int k = 0; k < 4; k++) {
+    const double r = block_sum(acc[k], sh);
+    if (threadIdx.x == 0) partial[k * REDUCE_BLOCKS + blockIdx.x] = r;
+  }
+}
+
+__global__ void __launch_bounds__(256) reduce_final_kernel(double *__restrict__ partial) {
+  __shared__ double sh[8];
+  for (int k = 0; k < 4; k++) {
+    double v = 0.0;
+    for (int i = threadIdx.x; i < REDUCE_BLOCKS; i += blockDim.x) v += partial[k * REDUCE_BLOCKS + i];
+    const double r = block_sum(v, sh);
+    if (threadIdx.x == 0) partial[4 * REDUCE_BLOCKS + k] = r;
+  }
+}
+
+cudaError_t launch_reduce(const Geom &g, const double *fc, const uint8_t *mask, double *partial, cudaStream_t s) {
+  reduce_sites_kernel<<<REDUCE_BLOCKS, 256, 0, s>>>(g, fc, mask, partial);
+  reduce_final_kernel<<<1, 256, 0, s>>>(partial);
+  return cudaGetLastError();
+}
+
+}  // namespace dlbc

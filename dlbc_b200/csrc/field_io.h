@@ -1,0 +1,36 @@
+// field_io.h -- launchers of the layout-conversion, output and reduction kernels (field_io.cu).
+// None of these is on the per-step hot path.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include "lattice.cuh"
+
+namespace dlbc {
+
+constexpr int REDUCE_BLOCKS = 1184;  // 8 per SM on a 148-SM B200; fixed so reductions are deterministic
+
+// Staged device arrays are dense and halo-free (the halo of the host's Field.arr is stripped or
+// skipped by the strided host<->device copy): `aos` = [xc][ny][nz][19] for x-layers x0..x0+xc.
+cudaError_t launch_aos_to_soa(const Geom &g, const double *aos, int xc, int x0, double *soa_a, double *soa_b,
+                              cudaStream_t s);
+cudaError_t launch_soa_to_aos(const Geom &g, const double *soa, int xc, int x0, double *aos, cudaStream_t s);
+
+// mask: dense int32 [nx][ny][nz] <-> uint8 [zg][y][x]
+cudaError_t launch_mask_in(const Geom &g, const int32_t *in, uint8_t *out, int *flags, cudaStream_t s);
+cudaError_t launch_mask_out(const Geom &g, const uint8_t *in, int32_t *out, cudaStream_t s);
+
+// ghost planes when the slab is its own z neighbour (nranks == 1)
+cudaError_t launch_ghost_fill(const Geom &g, double *f, int narrays, cudaStream_t s);
+cudaError_t launch_ghost_fill_mask(const Geom &g, uint8_t *m, cudaStream_t s);
+
+// derived outputs into a dense, halo-free device array [nx][ny][nz][K]
+// kind 0 density(c1), 1 colour(c1 - c2), 2 raw velocity(c1), 3 copy of an SoA vector field [3][sites_g]
+cudaError_t launch_output(const Geom &g, int kind, const double *f, const uint8_t *mask, int c1, int c2, double *out,
+                          cudaStream_t s);
+// own-site density of every site incl. ghosts (SoA -> SoA), for the wall term
+cudaError_t launch_site_density(const Geom &g, const double *fc, double *rho, cudaStream_t s);
+
+// mass and momentum of one component over physical fluid sites: partial[4*REDUCE_BLOCKS + k], k = 0..3
+cudaError_t launch_reduce(const Geom &g, const double *fc, const uint8_t *mask, double *partial, cudaStream_t s);
+
+}  // namespace dlbc

@@ -1,0 +1,175 @@
+// lb_site.cuh -- per-site D3Q19 arithmetic shared by all step kernels (device code).
+//
+// Every function states the reference code it reproduces (paths relative to
+// /root/reference/src/dlbc/).  Operation ORDER follows the reference so that, compiled with
+// -fmad=false, results are bit-identical to the reference's fp64 arithmetic wherever EXACT
+// arithmetic is selected (the only exception is exp(), <= 1 ulp).  Terms multiplied by a zero
+// velocity component are skipped and +-1 multiplications become add/subtract: both are exact
+// identities for finite values, so skipping them does not change a single bit.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace dlbc {
+
+constexpr int Q = 19;
+constexpr int MAXC = 4;
+
+// lb/connectivity.d:401-418 (generateD3Q19)
+__host__ __device__ constexpr int cx(int q) {
+  constexpr int t[Q] = {0, 1, -1, 0, 0, 0, 0, 1, -1, 0, 0, 1, 1, 1, -1, 0, 0, -1, -1};
+  return t[q];
+}
+__host__ __device__ constexpr int cy(int q) {
+  constexpr int t[Q] = {0, 0, 0, 1, -1, 0, 0, 1, 1, 1, -1, 0, 0, -1, -1, 1, -1, 0, 0};
+  return t[q];
+}
+__host__ __device__ constexpr int cz(int q) {
+  constexpr int t[Q] = {0, 0, 0, 0, 0, 1, -1, 0, 0, 1, 1, 1, -1, 0, 0, -1, -1, 1, -1};
+  return t[q];
+}
+// lb/connectivity.d:128-142 (generateBounce): index of -c_q
+__host__ __device__ constexpr int bounce(int q) {
+  constexpr int t[Q] = {0, 2, 1, 4, 3, 6, 5, 14, 13, 16, 15, 18, 17, 8, 7, 10, 9, 12, 11};
+  return t[q];
+}
+// lb/connectivity.d:253-257
+__host__ __device__ constexpr double weight(int q) {
+  return q == 0 ? 1.0 / 3.0 : (q < 7 ? 1.0 / 18.0 : 1.0 / 36.0);
+}
+
+struct StepParams {
+  int ncomp;
+  double tau[MAXC];
+  double omega[MAXC];        // 1.0 / tau                          (collision.d:99)
+  double one_minus_omega[MAXC];
+  double inv_tau[MAXC];      // == omega; used when tau_pow2 (exact) or in FAST mode
+  int tau_pow2[MAXC];        // tau is a power of two: x / tau == x * (1/tau) exactly
+  double gcc[MAXC * MAXC];
+  double gwc[MAXC];
+  double gacc[3];
+  int any_gwc;
+};
+
+// lb/density.d:37-39: Phobos std.algorithm.sum on a random-access fp range is PAIRWISE:
+// s(r) = len <= 2 ? direct : s(r[0..len/2]) + s(r[len/2..len]).  For 19 elements:
+//   [0,9) = ((f0+f1)+(f2+f3)) + ((f4+f5)+(f6+(f7+f8)))
+//   [9,19) = ((f9+f10)+(f11+(f12+f13))) + ((f14+f15)+(f16+(f17+f18)))
+// Pinned by the reference's golden population -> density files (tests/test_oracle_golden.py).
+__device__ __forceinline__ double density19(const double (&f)[Q]) {
+  const double a = ((f[0] + f[1]) + (f[2] + f[3])) + ((f[4] + f[5]) + (f[6] + (f[7] + f[8])));
+  const double b = ((f[9] + f[10]) + (f[11] + (f[12] + f[13]))) + ((f[14] + f[15]) + (f[16] + (f[17] + f[18])));
+  return a + b;
+}
+
+// lb/momentum.d:39-49 / velocity.d:37-48 numerator: m[d] = sum_q f[q]*c_q[d], sequential over q
+// from 0.0 (zero terms skipped, +-1 as add/sub).
+__device__ __forceinline__ void momentum19(const double (&f)[Q], double (&m)[3]) {
+  m[0] = 0.0; m[1] = 0.0; m[2] = 0.0;
+#pragma unroll
+  for (int q = 0; q < Q; q++) {
+    if (cx(q) == 1) m[0] += f[q]; else if (cx(q) == -1) m[0] -= f[q];
+    if (cy(q) == 1) m[1] += f[q]; else if (cy(q) == -1) m[1] -= f[q];
+    if (cz(q) == 1) m[2] += f[q]; else if (cz(q) == -1) m[2] -= f[q];
+  }
+}
+
+// lb/force.d:320-332
+template <int PSI>
+__device__ __forceinline__ double psi_of(double rho) {
+  if (PSI == 0) return rho;
+  return 1.0 - exp(-rho);
+}
+
+template <bool EXACT>
+__device__ __forceinline__ double div_by(double x, double y, double inv_y) {
+  return EXACT ? x / y : x * inv_y;
+}
+
+// lb/eqdist.d:69-100 (SecondOrder / ThirdOrder).  `m` is the raw momentum sum (velocity.d:40-45),
+// divided by rho0 here (velocity.d:46).
+template <int FORM, bool EXACT>
+__device__ __forceinline__ void eqdist_poly(const double (&m)[3], const double (&dv)[3], double rho0,
+                                            double (&dist)[Q]) {
+  const double css = 1.0 / 3.0;
+  const double css2 = 2.0 * css;
+  const double css2p2 = css2 * css;
+  const double css6p3 = 3.0 * css2p2 * css;
+  const double inv_rho = EXACT ? 0.0 : 1.0 / rho0;
+  double v[3];
+#pragma unroll
+  for (int d = 0; d < 3; d++) v[d] = dv[d] + div_by<EXACT>(m[d], rho0, inv_rho);
+  const double vdotv = ((0.0 + v[0] * v[0]) + v[1] * v[1]) + v[2] * v[2];
+  const double t_vv = div_by<EXACT>(vdotv, css2, 1.0 / css2);
+#pragma unroll
+  for (int q = 0; q < Q; q++) {
+    // dotProduct (range.d:57-67): sum0 = 0; sum0 += v[d] * c[d]
+    double vc = 0.0;
+    if (cx(q) == 1) vc += v[0]; else if (cx(q) == -1) vc -= v[0];
+    if (cy(q) == 1) vc += v[1]; else if (cy(q) == -1) vc -= v[1];
+    if (cz(q) == 1) vc += v[2]; else if (cz(q) == -1) vc -= v[2];
+    double poly = 1.0 + div_by<EXACT>(vc, css, 1.0 / css) + div_by<EXACT>(vc * vc, css2p2, 1.0 / css2p2) - t_vv;
+    if (FORM == 1) {
+      poly = poly + div_by<EXACT>(vc * vc * vc, css6p3, 1.0 / css6p3) - div_by<EXACT>(vdotv * vc, css2p2, 1.0 / css2p2);
+    }
+    dist[q] = rho0 * weight(q) * poly;
+  }
+}
+
+// lb/eqdist.d:101-184 (BDist2, D3Q19): LB3D-compatible third-order form in dv only.
+__device__ __forceinline__ void eqdist_bdist2(const double (&dv)[3], double rho0, double (&dist)[Q]) {
+  const double aN1 = 1.0 / 36.0;
+  const double aN0 = 1.0 / 3.0;
+  const double haN1 = 0.5 * aN1;
+  const double aN1_6 = aN1 / 6.0;
+  const double T = 1.0 / 3.0;
+  const double holdit = 1.0 / T;
+  const double tux = dv[0], tuy = dv[1], tuz = dv[2];
+  const double tuxt = tux * holdit, tuyt = tuy * holdit, tuzt = tuz * holdit;
+  const double uke = 0.5 * (tux * tuxt + tuy * tuyt + tuz * tuzt);
+  const double cst = 1.0 - uke;
+  const double const1 = aN1 * cst;
+  double cdotu, even, odd;
+#define DLBC_PAIR(expr, qp, qm, twice)                       \
+  cdotu = (expr);                                            \
+  even = const1 + haN1 * cdotu * cdotu;                      \
+  odd = const1 * cdotu + aN1_6 * cdotu * cdotu * cdotu;      \
+  dist[qp] = twice ? 2.0 * (even + odd) : (even + odd);      \
+  dist[qm] = twice ? 2.0 * (even - odd) : (even - odd);
+  DLBC_PAIR(tuxt, 1, 2, true)
+  DLBC_PAIR(tuyt, 3, 4, true)
+  DLBC_PAIR(tuzt, 5, 6, true)
+  DLBC_PAIR(tuxt + tuyt, 7, 14, false)
+  DLBC_PAIR(tuxt - tuyt, 13, 8, false)
+  DLBC_PAIR(tuxt + tuzt, 11, 18, false)
+  DLBC_PAIR(tuxt - tuzt, 12, 17, false)
+  DLBC_PAIR(tuyt + tuzt, 9, 16, false)
+  DLBC_PAIR(tuyt - tuzt, 15, 10, false)
+#undef DLBC_PAIR
+  dist[0] = aN0 * cst;
+#pragma unroll
+  for (int q = 0; q < Q; q++) dist[q] *= rho0;
+}
+
+// lb/collision.d:100-116: dv, equilibrium, BGK relaxation of one component at one site.
+// F = Shan-Chen force on this component (force.d), m = raw momentum of f, u = BDist2 common
+// velocity (collision.d:156-196; ignored otherwise).
+template <int EQ, bool EXACT>
+__device__ __forceinline__ void collide_site(double (&f)[Q], double rho, const double (&m)[3],
+                                             const double (&F)[3], const double (&u)[3],
+                                             const StepParams &P, int c) {
+  double dv[3];
+  const double inv_rho = EXACT ? 0.0 : 1.0 / rho;
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    dv[d] = P.tau[c] * (P.gacc[d] + div_by<EXACT>(F[d], rho, inv_rho));
+    if (EQ == 2) dv[d] += u[d];
+  }
+  double eq[Q];
+  if (EQ == 2) eqdist_bdist2(dv, rho, eq);
+  else eqdist_poly<EQ, EXACT>(m, dv, rho, eq);
+  const double omega = P.omega[c], om1 = P.one_minus_omega[c];
+#pragma unroll
+  for (int q = 0; q < Q; q++) f[q] = f[q] * om1 + omega * eq[q];
+}
+
+}  // namespace dlbc

@@ -1,0 +1,49 @@
+// step_cN.inl -- instantiates the two-pass kernels for DLBC_NC components (included by step_c*.cu)
+#include "kernels.h"
+#include "step_two_pass.cuh"
+
+namespace dlbc {
+
+#define DLBC_CAT2(a, b) a##b
+#define DLBC_CAT(a, b) DLBC_CAT2(a, b)
+
+static inline dim3 block_for(const Geom &g) { return dim3(g.nx >= 128 ? 128 : ((g.nx + 31) / 32) * 32); }
+static inline dim3 grid_for(const Geom &g, dim3 b, int z_count) { return dim3((g.nx + b.x - 1) / b.x, g.ny, z_count); }
+
+cudaError_t DLBC_CAT(launch_psi_c, DLBC_NC)(const StepLaunch &L, int z_begin, int z_count) {
+  constexpr int C = DLBC_NC;
+  const dim3 b = block_for(L.g), gr = grid_for(L.g, b, z_count);
+#define PSI_CASE(PSI, MASK) psi_kernel<C, PSI, MASK><<<gr, b, 0, L.stream>>>(L.g, L.f, z_begin)
+  if (L.psi == 0) { if (L.mask) PSI_CASE(0, true); else PSI_CASE(0, false); }
+  else            { if (L.mask) PSI_CASE(1, true); else PSI_CASE(1, false); }
+#undef PSI_CASE
+  return cudaGetLastError();
+}
+
+template <int C, int EQ, bool SC>
+static void fused_dispatch(const StepLaunch &L, dim3 gr, dim3 b, int z_begin) {
+  if (L.mask) {
+    if (L.exact) fused_kernel<C, EQ, SC, true, true><<<gr, b, 0, L.stream>>>(L.g, L.f, L.p, z_begin);
+    else         fused_kernel<C, EQ, SC, true, false><<<gr, b, 0, L.stream>>>(L.g, L.f, L.p, z_begin);
+  } else {
+    if (L.exact) fused_kernel<C, EQ, SC, false, true><<<gr, b, 0, L.stream>>>(L.g, L.f, L.p, z_begin);
+    else         fused_kernel<C, EQ, SC, false, false><<<gr, b, 0, L.stream>>>(L.g, L.f, L.p, z_begin);
+  }
+}
+
+cudaError_t DLBC_CAT(launch_fused_c, DLBC_NC)(const StepLaunch &L, int z_begin, int z_count) {
+  constexpr int C = DLBC_NC;
+  const dim3 b = block_for(L.g), gr = grid_for(L.g, b, z_count);
+  switch (L.eq * 2 + (L.sc ? 1 : 0)) {
+    case 0: fused_dispatch<C, 0, false>(L, gr, b, z_begin); break;
+    case 1: fused_dispatch<C, 0, true>(L, gr, b, z_begin); break;
+    case 2: fused_dispatch<C, 1, false>(L, gr, b, z_begin); break;
+    case 3: fused_dispatch<C, 1, true>(L, gr, b, z_begin); break;
+    case 4: fused_dispatch<C, 2, false>(L, gr, b, z_begin); break;
+    case 5: fused_dispatch<C, 2, true>(L, gr, b, z_begin); break;
+    default: return cudaErrorInvalidValue;
+  }
+  return cudaGetLastError();
+}
+
+}  // namespace dlbc

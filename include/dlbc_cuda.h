@@ -1,0 +1,157 @@
+/*
+ * dlbc_cuda.h -- C ABI of libdlbc_cuda.so: DLBC's lattice-Boltzmann timestep on B200 (sm_100a).
+ *
+ * This is the drop-in boundary for ONE path of DLBC: the per-timestep sequence of
+ * runTimeloop (reference src/main.d:179-195): exchangeHalo -> advectFields -> resetForce ->
+ * addShanChenForce -> distributeForce -> prepareToCollide -> collideFields, for the D3Q19
+ * lattice, N-component Shan-Chen, BGK, bounce-back walls, periodic boundaries.  Parameter files,
+ * plugin registration, mask/geometry setup, initial conditions and HDF5 output stay on the
+ * host (D) side; they hand finished arrays to this library and fetch results from it.
+ *
+ * Conventions (modelled on how the reference treats its C libraries, src/dlbc/mpi.d:16-18 and
+ * src/dlbc/io/hdf5.d:54-57): plain C types only; every function returns int, 0 = success,
+ * non-zero = failure with a message available from dlbc_cuda_last_error(); the library never
+ * calls exit().  One host thread drives one context (the reference's ranks are single
+ * threaded); contexts are not thread-safe; there is no global mutable state besides the
+ * last-error string of failed dlbc_cuda_create calls.  There is NO CPU fallback: without a
+ * CUDA device every compute entry point fails.
+ *
+ * Host array layouts are exactly the reference's Field.arr (src/dlbc/fields/field.d:114-125):
+ * C order, populations AoS double[x][y][z][19], scalars [x][y][z], vectors [x][y][z][3], mask
+ * int32 (enum Mask: None = 0, Solid = 1; src/dlbc/lb/mask.d:84-93), with `halo` extra sites on
+ * every side of every dimension (2 from the D host, 0 is accepted for convenience).  The
+ * library keeps populations on the device as fp64 structure-of-arrays f[c][q][z][y][x].
+ *
+ * Decomposition: z-slabs.  Rank r of nranks owns global z in [r*gn[2]/nranks, (r+1)*gn[2]/nranks)
+ * and all of x and y, i.e. the reference's M.nc = [1, 1, nranks], M.c = [0, 0, r]
+ * (src/dlbc/parallel.d:190-237).  One process (or thread) per GPU, one context each.
+ */
+#ifndef DLBC_CUDA_H
+#define DLBC_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DLBC_CUDA_ABI_VERSION 1
+#define DLBC_CUDA_MAX_COMPONENTS 4
+#define DLBC_CUDA_NCCL_ID_BYTES 128
+
+/* enum PsiForm, src/dlbc/lb/force.d:48-57 */
+enum { DLBC_PSI_LINEAR = 0, DLBC_PSI_EXPONENTIAL = 1 };
+/* enum EqDistForm, src/dlbc/lb/eqdist.d:23-36 */
+enum { DLBC_EQDIST_SECOND_ORDER = 0, DLBC_EQDIST_THIRD_ORDER = 1, DLBC_EQDIST_BDIST2 = 2 };
+/* arithmetic mode */
+enum {
+  DLBC_ARITH_FAST = 0,  /* divisions by constants/shared denominators become reciprocal multiplies
+                           (<= 1 ulp per operation; within the 1e-12 parity tolerance) */
+  DLBC_ARITH_EXACT = 1  /* every fp64 operation as the reference performs it (IEEE divisions, same
+                           order): bit-identical to the CPU restatement except for exp() */
+};
+/* step kernel variants (evidence for the design choice; results are identical) */
+enum {
+  DLBC_KERNEL_AUTO = 0,
+  DLBC_KERNEL_TWO_PASS = 1,   /* psi kernel + fused pull/force/collide kernel (psi via L1/L2) */
+  DLBC_KERNEL_ZMARCH = 2      /* single pass: z-marching fused kernel, psi planes in shared memory */
+};
+
+/* Replaces: the module-level parameters the timestep reads -- lattice.gn (lattice.d:28),
+ * lb.components, lb.tau (lb/lb.d), lb.force.{globalAcc,enableShanChen,gcc,gwc,psiForm}
+ * (lb/force.d:26-43), lb.eqdist.eqDistForm (lb/eqdist.d:18), parallel.nc (parallel.d:34). */
+typedef struct dlbc_cuda_config {
+  int32_t abi_version;            /* DLBC_CUDA_ABI_VERSION */
+  int32_t d, q;                   /* must be 3, 19 (connectivity.d:21-32 default gconn) */
+  int64_t gn[3];                  /* global physical lattice size */
+  int32_t ncomp;                  /* 1..DLBC_CUDA_MAX_COMPONENTS */
+  double tau[DLBC_CUDA_MAX_COMPONENTS];
+  double gcc[DLBC_CUDA_MAX_COMPONENTS * DLBC_CUDA_MAX_COMPONENTS]; /* row-major [f1][f2] */
+  double gwc[DLBC_CUDA_MAX_COMPONENTS];
+  double global_acc[3];
+  int32_t psi_form;
+  int32_t eqdist_form;
+  int32_t enable_shan_chen;
+  int32_t arithmetic;             /* DLBC_ARITH_* */
+  int32_t kernel_variant;         /* DLBC_KERNEL_* */
+  int32_t device;                 /* CUDA device ordinal for this context */
+  int32_t rank, nranks;           /* z-slab index / count; nranks = 1: periodic in-process */
+  uint8_t nccl_id[DLBC_CUDA_NCCL_ID_BYTES]; /* from dlbc_cuda_nccl_unique_id on rank 0, broadcast
+                                               by the host (MPI_Bcast in D); unused if nranks = 1 */
+} dlbc_cuda_config;
+
+typedef struct dlbc_cuda_ctx dlbc_cuda_ctx;
+
+/* ---- lifecycle ------------------------------------------------------------------------------
+ * create replaces LType(gn, components, ...), prepareLBFields, prepareForce (main.d:119-124,
+ * lb/init.d:60-72, lb/force.d:67-107): validates the parameters as prepareForce does, selects
+ * the device, allocates the device fields.  Collective over all ranks when nranks > 1. */
+int dlbc_cuda_abi_version(void);
+int dlbc_cuda_device_count(int *count);
+int dlbc_cuda_nccl_unique_id(uint8_t id[DLBC_CUDA_NCCL_ID_BYTES]);
+int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out);
+int dlbc_cuda_destroy(dlbc_cuda_ctx *ctx);                 /* endMpi-time teardown */
+const char *dlbc_cuda_last_error(const dlbc_cuda_ctx *ctx); /* ctx may be NULL (create failures) */
+
+/* Pinned host memory for the arrays handed to upload/download (optional; any host memory works,
+ * pinned memory makes the copies asynchronous and faster). */
+int dlbc_cuda_host_alloc(void **ptr, size_t bytes);
+int dlbc_cuda_host_free(void *ptr);
+
+/* ---- state transfer -------------------------------------------------------------------------
+ * upload_populations replaces the result of initFluids / readCheckpoint (lb/init.d:77-136,
+ * io/checkpoint.d:80-103) for L.fluids[comp]; download_populations is what
+ * dumpField("population-...") and dumpCheckpoint read (lb/io.d:58-62).  `aos` is this rank's
+ * local block, Field.arr._data.ptr when halo = 2.  Only physical sites are transferred; the
+ * library maintains its own ghost planes.  The *_xrange forms move x-layers
+ * [x_begin, x_begin + x_count) only (`aos` then points at the first of those layers), so a host
+ * can stream a lattice that does not fit in its memory. */
+int dlbc_cuda_upload_populations(dlbc_cuda_ctx *ctx, int comp, const double *aos, int halo);
+int dlbc_cuda_download_populations(dlbc_cuda_ctx *ctx, int comp, double *aos, int halo);
+int dlbc_cuda_upload_populations_xrange(dlbc_cuda_ctx *ctx, int comp, const double *aos, int halo,
+                                        int64_t x_begin, int64_t x_count);
+int dlbc_cuda_download_populations_xrange(dlbc_cuda_ctx *ctx, int comp, double *aos, int halo,
+                                          int64_t x_begin, int64_t x_count);
+/* upload_mask replaces the result of initMask (lb/mask.d:134-172); values must be 0 or 1. */
+int dlbc_cuda_upload_mask(dlbc_cuda_ctx *ctx, const int32_t *mask, int halo);
+int dlbc_cuda_download_mask(dlbc_cuda_ctx *ctx, int32_t *mask, int halo);
+
+/* ---- the hot path ---------------------------------------------------------------------------
+ * step replaces the statements of runTimeloop, main.d:179-195, nsteps times.  Asynchronous:
+ * returns after enqueueing on the context's streams; sync waits (and reports device errors). */
+int dlbc_cuda_step(dlbc_cuda_ctx *ctx, int nsteps);
+int dlbc_cuda_sync(dlbc_cuda_ctx *ctx);
+int64_t dlbc_cuda_timestep(const dlbc_cuda_ctx *ctx); /* steps done since create */
+
+/* ---- outputs (dumpLBData, lb/io.d:56-101) -- state after the last completed step -------------
+ * density: densityField (density.d:89-96); colour: colourField (density.d:284-295), zero on
+ * solid sites; velocity: rawVelocityField (velocity.d:106-117), zero on solid sites; force:
+ * L.force[comp] of the last step (zero before the first step and on solid sites).  Physical
+ * sites only; with halo > 0 the halo of `out` is left untouched. */
+int dlbc_cuda_download_density(dlbc_cuda_ctx *ctx, int comp, double *out, int halo);
+int dlbc_cuda_download_colour(dlbc_cuda_ctx *ctx, int comp1, int comp2, double *out, int halo);
+int dlbc_cuda_download_velocity(dlbc_cuda_ctx *ctx, int comp, double *out, int halo);
+int dlbc_cuda_download_force(dlbc_cuda_ctx *ctx, int comp, double *out, int halo);
+/* globalTotalMass (density.d:172-180) / globalTotalMomentum (momentum.d:172-180): sums over
+ * physical fluid sites of all ranks; deterministic tree reduction (not the reference's
+ * sequential order, so equal only to summation round-off). */
+int dlbc_cuda_total_mass(dlbc_cuda_ctx *ctx, int comp, double *out);
+int dlbc_cuda_total_momentum(dlbc_cuda_ctx *ctx, int comp, double out[3]);
+
+/* ---- introspection / measurement --------------------------------------------------------------
+ * tables: the device's copy of connectivity.d:401-418 / :198-212 / :253-257 (velocities[19][3],
+ * bounce[19], weights[19], css).  launch_count: kernels launched by this context so far.
+ * timed_steps: run nsteps between two CUDA events recorded on the context's compute stream and
+ * return the elapsed milliseconds (synchronous).  kernel_times: run one step with events around
+ * every kernel; fills names/ms for up to `cap` kernels and returns how many in *n. */
+int dlbc_cuda_tables(int64_t *velocities, int64_t *bounce, double *weights, double *css);
+int dlbc_cuda_launch_count(const dlbc_cuda_ctx *ctx, int64_t *count);
+int dlbc_cuda_timed_steps(dlbc_cuda_ctx *ctx, int nsteps, double *elapsed_ms);
+int dlbc_cuda_kernel_times(dlbc_cuda_ctx *ctx, int cap, const char **names, double *ms, int *n);
+int dlbc_cuda_device_bytes(const dlbc_cuda_ctx *ctx, int64_t *bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLBC_CUDA_H */
