@@ -1,0 +1,352 @@
+#!/usr/bin/env python
+"""bench.py -- MLUPS of the DLBC timestep (D3Q19, two-component Shan-Chen) on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One JSON line on stdout (rank 0).  A "step" is one lattice-Boltzmann timestep (the statements of
+runTimeloop, reference src/main.d:179-195) over the whole lattice.
+
+* workload (N = 1): BASELINE.json configs[2], D3Q19 two-component Shan-Chen spinodal decomposition
+  at 512^3 (the configuration the metric is quoted on); N > 1: weak scaling, 512^3 per GPU as
+  z-slabs of a 512 x 512 x (512 N) lattice, ghost planes exchanged with NCCL send/recv.
+* value: MLUPS = 1e-6 * nx*ny*nz * K / t (reference definition, src/dlbc/timers.d:222-230), state
+  resident in HBM, t from CUDA events on the compute stream, max over ranks.
+* e2e: the same metric for the whole job a host program runs through the C ABI with HOST buffers:
+  upload of the initial populations from pinned host memory + K steps + download of the density
+  fields (what dumpLBData writes), all inside the timed region.
+* roofline: algorithmic bytes per site update (2*C*19*8 + 1 = 609 B at C = 2) over the dominant
+  kernel's CUDA-event duration, against MEASURED_PEAKS.json's copy bandwidth.
+* cpu_baseline / --impl reference: the CPU restatement of the reference timestep (oracle/, "port":
+  the D reference cannot be built in this image) on the box's host cores, bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "MLUPS (D3Q19 2-comp Shan-Chen)"
+B_ALG = {1: 2 * 1 * 19 * 8 + 1, 2: 2 * 2 * 19 * 8 + 1}
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(device), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return None
+        time.sleep(0.05)
+        self.p.terminate()
+        try:
+            out, _ = self.p.communicate(timeout=5)
+        except Exception:
+            self.p.kill()
+            return None
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return None
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---- CPU arm: the oracle port on the host cores ---------------------------------------------------
+def cpu_port_mlups(sample_n, steps, warmup, ncomp=2):
+    """The reference's CPU algorithm (oracle/ restatement) on a sample_n^3 sample of the workload."""
+    from dlbc_b200 import cases
+    from oracle import oracle as O
+    cores = os.cpu_count() or 1
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except Exception:
+        pass
+    params, pops, _ = cases.spinodal(sample_n)
+    p = dict(params)
+    gn, nc = p.pop("gn"), p.pop("components")
+    L = O.OracleLattice(gn, nc, **p, nthreads=cores)
+    for c, a in enumerate(pops):
+        L.set_populations(c, a)
+    L.exchange_halo()
+    L.step(max(1, warmup))
+    t0 = time.perf_counter()
+    L.step(steps)
+    dt = time.perf_counter() - t0
+    return sample_n ** 3 * steps / dt * 1e-6, dt, cores
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    n = args.cpu_sample
+    # size the timed run to a few tens of seconds: calibrate on 2 steps
+    mlups, dt, cores = cpu_port_mlups(n, 2, 1)
+    per_step = dt / 2
+    steps = max(args.steps, 1)
+    budget = 120.0
+    if steps * per_step > budget:
+        n = max(32, int(n * (budget / (steps * per_step)) ** (1 / 3)) // 16 * 16)
+    mlups, dt, cores = cpu_port_mlups(n, steps, min(args.warmup, 3))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": mlups, "unit": "MLUPS", "n_gpus": args.gpus,
+        "steps": steps, "warmup": min(args.warmup, 3), "ms_per_step": 1e3 * dt / steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "D3Q19 two-component Shan-Chen spinodal decomposition (BASELINE configs[2])",
+                   "lattice": [n, n, n], "components": 2, "note": "CPU restatement of the DLBC timestep "
+                   "(oracle/, OpenMP x-slabs standing in for MPI ranks); the D reference needs dmd/ldc/gdc + MPICH + "
+                   "parallel HDF5, none of which exist in this image"},
+        "cpu_baseline": {"value": mlups, "unit": "MLUPS", "cores": cores, "kind": "port",
+                         "sample": f"{n}^3 sample of the 512^3 workload, {steps} timesteps"},
+        "e2e": {"value": mlups, "unit": "MLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---- GPU arm -----------------------------------------------------------------------------------------
+def fill_lattice(G, gn_local, ncomp, pinned_views, timed=False):
+    """Upload a perturbed-equilibrium state layer block by layer block through the C ABI."""
+    nx = gn_local[0]
+    xc = pinned_views[0].shape[0]
+    nbytes = 0
+    for c in range(ncomp):
+        for i, x0 in enumerate(range(0, nx, xc)):
+            cnt = min(xc, nx - x0)
+            blk = pinned_views[(c + i) % len(pinned_views)]
+            G.set_populations_xrange(c, blk[:cnt], x0)
+            nbytes += blk[:cnt].nbytes
+    return nbytes
+
+
+def pinned_array(lib, shape):
+    import ctypes as C
+    n = int(np.prod(shape)) * 8
+    ptr = C.c_void_p()
+    rc = lib.dlbc_cuda_host_alloc(C.byref(ptr), n)
+    if rc:
+        raise RuntimeError("dlbc_cuda_host_alloc failed")
+    buf = (C.c_double * (n // 8)).from_address(ptr.value)
+    return np.frombuffer(buf, dtype=np.float64).reshape(shape), ptr
+
+
+def run_ours(args, rank, world, local_rank):
+    from dlbc_b200 import cases, init as I
+    from dlbc_b200 import lib as dlib
+    from dlbc_b200.lattice import Lattice
+
+    dist = None
+    nccl_id = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        idt = torch.zeros(dlib.NCCL_ID_BYTES, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(dlib.nccl_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        nccl_id = bytes(idt.cpu().numpy().tobytes())
+
+    n = args.size
+    ncomp = args.components
+    gn = (n, n, n * world)
+    params = dict(cases.SC2) if ncomp == 2 else dict(tau=[1.0], eqdist_form="SecondOrder", enable_shan_chen=False)
+    G = Lattice(gn, ncomp, **params, arithmetic=args.arith, kernel=args.kernel, device=local_rank,
+                rank=rank, nranks=world, nccl_id=nccl_id)
+    gl = G.n
+    sites_local = gl[0] * gl[1] * gl[2]
+    sites_total = sites_local * world
+
+    # synthetic initial state: a few distinct pinned layer blocks, reused cyclically
+    lib = dlib.load()
+    layer_bytes = gl[1] * gl[2] * 19 * 8
+    xc = max(1, min(gl[0], (160 << 20) // layer_bytes))
+    form = I.BDIST2 if ncomp == 2 else I.SECOND_ORDER
+    rho0 = 0.37 if ncomp == 2 else 1.0
+    views, ptrs = [], []
+    for k in range(2):
+        v, p = pinned_array(lib, (xc, gl[1], gl[2], 19))
+        v[...] = cases.synthetic_layers(gl, xc, rho0, 0.01, form, 42 + 7 * rank + k)
+        views.append(v); ptrs.append(p)
+    fill_lattice(G, gl, ncomp, views)
+    G.sync()
+
+    def barrier():
+        G.sync()
+        if dist is not None:
+            dist.barrier()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        import torch
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident timing: W warm-up steps, then exactly K timed steps ----
+    G.step(args.warmup)
+    barrier()
+    launches0 = G.launch_count
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    ms = G.timed_steps(args.steps)
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    launches = G.launch_count - launches0
+    ms = max_over_ranks(ms)
+    value = sites_total * args.steps / (ms * 1e-3) * 1e-6
+
+    # ---- dominant kernel, CUDA events around every launch (single-rank schedule only) ----
+    roof = None
+    peak, peak_src = measured_peak()
+    b_alg = B_ALG.get(ncomp, 2 * ncomp * 19 * 8 + 1)
+    if world == 1:
+        acc = {}
+        reps = max(3, min(args.steps, 10))
+        for _ in range(reps):
+            for name, t in G.kernel_times():
+                acc.setdefault(name, []).append(t)
+        dom = max(acc, key=lambda k: sum(acc[k]))
+        dom_ms = sum(acc[dom]) / len(acc[dom])
+        achieved = b_alg * sites_local / (dom_ms * 1e-3) * 1e-9
+        roof = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "alg_bytes_per_site": b_alg, "kernel_ms": dom_ms,
+                "kernels_ms": {k: sum(v) / len(v) for k, v in acc.items()},
+                "step_frac": b_alg * sites_local / (ms / args.steps * 1e-3) * 1e-9 / peak,
+                "frac_of_8TBs_nominal": achieved / 8000.0}
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            try:
+                with open(tp) as f:
+                    roof["traffic"] = json.load(f).get(dom)
+            except Exception:
+                pass
+    else:
+        achieved = b_alg * sites_local / (ms / args.steps * 1e-3) * 1e-9
+        roof = {"bound": "hbm", "kernel": "whole step (per GPU)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "alg_bytes_per_site": b_alg}
+
+    # ---- end to end through the C ABI with host buffers ----
+    e2e = None
+    if not args.no_e2e:
+        import ctypes as C
+        dens, dptr = pinned_array(lib, gl)
+        barrier()
+        t0 = time.perf_counter()
+        h2d = fill_lattice(G, gl, ncomp, views)
+        G.step(args.steps, sync=False)
+        d2h = 0
+        for c in range(ncomp):
+            G._ck(lib.dlbc_cuda_download_density(G._h, c, dens.ctypes.data_as(C.POINTER(C.c_double)), 0))
+            d2h += dens.nbytes
+        G.sync()
+        dt = time.perf_counter() - t0
+        dt = max_over_ranks(dt)
+        e2e = {"value": sites_total * args.steps / dt * 1e-6, "unit": "MLUPS",
+               "h2d_bytes_per_step": h2d * world / args.steps, "d2h_bytes_per_step": d2h * world / args.steps,
+               "seconds": dt, "what": "pinned-host upload of all populations + K steps + download of all density fields"}
+        lib.dlbc_cuda_host_free(dptr)
+
+    mass = [G.total_mass(c) for c in range(ncomp)]
+    G.close()
+    for p in ptrs:
+        lib.dlbc_cuda_host_free(p)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        m, dt, cores = cpu_port_mlups(args.cpu_sample, args.cpu_steps, 1)
+        cpu = {"value": m, "unit": "MLUPS", "cores": cores, "kind": "port",
+               "sample": f"{args.cpu_sample}^3 sample of the workload, {args.cpu_steps} timesteps, {dt:.1f} s"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": "MLUPS", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": ("D3Q19 two-component Shan-Chen spinodal decomposition (BASELINE configs[2])"
+                                    if ncomp == 2 else "D3Q19 single-fluid BGK periodic (BASELINE configs[1])"),
+                       "lattice": list(gn), "components": ncomp, "decomposition": f"{world} z-slab(s) of {list(gl)}",
+                       "arithmetic": args.arith, "kernel": args.kernel,
+                       "l2": "inputs exceed L2 (populations are %.1f GB per GPU)" % (2 * ncomp * 19 * 8 * sites_local / 1e9)},
+            "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "total_mass": mass,
+        }
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--size", type=int, default=512, help="lattice edge per GPU")
+    ap.add_argument("--components", type=int, default=2)
+    ap.add_argument("--arith", default="fast", choices=["fast", "exact"])
+    ap.add_argument("--kernel", default="auto", choices=["auto", "two_pass", "zmarch"])
+    ap.add_argument("--cpu-sample", type=int, default=128)
+    ap.add_argument("--cpu-steps", type=int, default=20)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        log(f"note: WORLD_SIZE={world} but --gpus {args.gpus}; using WORLD_SIZE")
+    if args.impl == "reference":
+        run_reference(args, rank)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -17,9 +17,8 @@ struct dlbc_cuda_ctx {
   int device = 0;
   int variant = DLBC_KERNEL_TWO_PASS;
 
-  cudaStream_t compute = nullptr;  // step kernels
-  cudaStream_t comm = nullptr;     // ghost-plane exchange (NCCL)
-  cudaStream_t copy = nullptr;     // host <-> device staging
+  cudaStream_t compute = nullptr;  // step kernels, layout conversion, host <-> device copies
+  cudaStream_t comm = nullptr;     // per-step ghost-plane exchange (NCCL), overlapped with compute
 
   double *f[2] = {nullptr, nullptr};  // populations, A/B: [C][19][sites_g]
   int cur = 0;                        // f[cur] holds the current state
@@ -36,7 +35,6 @@ struct dlbc_cuda_ctx {
   size_t stage_bytes = 0;
   double *partial = nullptr;          // device, reduction partials
   int *flags = nullptr;               // device, [2]: bad mask value seen, solid count
-  int64_t xchunk = 16;                // x-layers per staged population chunk
 
   // multi-rank
   ncclComm *nccl = nullptr;
@@ -44,6 +42,10 @@ struct dlbc_cuda_ctx {
 
   // events for measurement
   cudaEvent_t ev_a = nullptr, ev_b = nullptr;
+  // cross-stream ordering of the multi-rank step (no timing)
+  cudaEvent_t ev_bnd = nullptr;        // compute: boundary planes written
+  cudaEvent_t ev_ghost_psi = nullptr;  // comm: psi ghost planes received
+  cudaEvent_t ev_ghost_f = nullptr;    // comm: population ghost planes of the new buffer received
   std::vector<cudaEvent_t> ev_pool;
 
   int64_t timestep = 0;

@@ -1,0 +1,817 @@
+// dlbc_cuda.cu -- implementation of the C ABI declared in include/dlbc_cuda.h.
+//
+// Host-side orchestration only: context lifecycle, layout conversion on upload/download, the
+// per-step launch schedule (single rank and z-slab multi rank with NCCL ghost-plane exchange
+// overlapped with the interior kernels), outputs and diagnostics.  All arithmetic lives in the
+// kernels (step_*.cuh, field_io.cu).  There is no CPU fallback anywhere in this file: every
+// compute entry point needs a CUDA device and fails with an error message otherwise.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "context.h"
+#include "field_io.h"
+#include "nccl_dyn.h"
+
+using namespace dlbc;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct KernelSet {
+  launch_fn psi;
+  force_fn force;
+  launch_fn fused[2];   // [exact]
+  launch_fn zmarch[2];  // [exact]
+};
+
+#define DLBC_SET(NC)                                                                                      \
+  { launch_psi_c##NC, launch_force_c##NC, {launch_fused_fast_c##NC, launch_fused_exact_c##NC},            \
+    {launch_zmarch_fast_c##NC, launch_zmarch_exact_c##NC} }
+const KernelSet kKernels[DLBC_CUDA_MAX_COMPONENTS] = {DLBC_SET(1), DLBC_SET(2), DLBC_SET(3), DLBC_SET(4)};
+#undef DLBC_SET
+
+int set_error(dlbc_cuda_ctx *ctx, const std::string &msg, int code) {
+  if (ctx) ctx->err = msg; else g_create_error = msg;
+  return code ? code : 1;
+}
+int cuda_fail(dlbc_cuda_ctx *ctx, const char *what, cudaError_t e) {
+  return set_error(ctx, std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")", 1000 + (int)e);
+}
+int nccl_fail(dlbc_cuda_ctx *ctx, const char *what, ncclResult_t r) {
+  const char *s = nccl_api().GetErrorString ? nccl_api().GetErrorString(r) : "?";
+  return set_error(ctx, std::string(what) + ": NCCL error " + std::to_string((int)r) + " (" + s + ")", 2000 + (int)r);
+}
+
+#define CK(expr)                                                   \
+  do {                                                             \
+    cudaError_t e_ = (expr);                                       \
+    if (e_ != cudaSuccess) return cuda_fail(ctx, #expr, e_);       \
+  } while (0)
+#define NK(expr)                                                   \
+  do {                                                             \
+    ncclResult_t r_ = (expr);                                      \
+    if (r_ != ncclSuccess) return nccl_fail(ctx, #expr, r_);       \
+  } while (0)
+#define TRY(expr)                \
+  do {                           \
+    int rc_ = (expr);            \
+    if (rc_) return rc_;         \
+  } while (0)
+#define ARG(cond, msg)                                                 \
+  do {                                                                 \
+    if (!(cond)) return set_error(ctx, std::string("dlbc_cuda: ") + msg, 1); \
+  } while (0)
+
+bool is_pow2(double x) {
+  int e;
+  return x > 0.0 && std::frexp(x, &e) == 0.5;
+}
+
+int64_t pop_arrays(const dlbc_cuda_ctx *ctx) { return (int64_t)ctx->cfg.ncomp * Q; }
+double *fcomp(dlbc_cuda_ctx *ctx, int buf, int comp) { return ctx->f[buf] + (int64_t)comp * Q * ctx->g.sites_g; }
+
+int ensure_stage(dlbc_cuda_ctx *ctx, size_t bytes) {
+  if (bytes <= ctx->stage_bytes) return 0;
+  if (ctx->stage) {
+    CK(cudaStreamSynchronize(ctx->compute));
+    CK(cudaFree(ctx->stage));
+    ctx->device_bytes -= (int64_t)ctx->stage_bytes;
+    ctx->stage = nullptr;
+    ctx->stage_bytes = 0;
+  }
+  CK(cudaMalloc(&ctx->stage, bytes));
+  ctx->stage_bytes = bytes;
+  ctx->device_bytes += (int64_t)bytes;
+  return 0;
+}
+
+int release_stage(dlbc_cuda_ctx *ctx) {
+  // large staging areas (outputs of a 512^3 lattice are GBs) are returned after use
+  if (ctx->stage && ctx->stage_bytes > ((size_t)256 << 20)) {
+    CK(cudaStreamSynchronize(ctx->compute));
+    CK(cudaFree(ctx->stage));
+    ctx->device_bytes -= (int64_t)ctx->stage_bytes;
+    ctx->stage = nullptr;
+    ctx->stage_bytes = 0;
+  }
+  return 0;
+}
+
+StepLaunch make_launch(dlbc_cuda_ctx *ctx, cudaStream_t s) {
+  StepLaunch L;
+  L.g = ctx->g;
+  L.f.f_old = ctx->f[ctx->cur];
+  L.f.f_new = ctx->f[1 - ctx->cur];
+  L.f.psi = ctx->psi;
+  L.f.rho_wall = ctx->rho_wall;
+  L.f.mask = ctx->mask;
+  L.p = ctx->p;
+  L.eq = ctx->cfg.eqdist_form;
+  L.psi = ctx->cfg.psi_form;
+  L.sc = ctx->cfg.enable_shan_chen;
+  L.mask = ctx->has_solid ? 1 : 0;
+  L.stream = s;
+  return L;
+}
+
+// ---- NCCL ghost-plane exchange: replaces exchangeHalo (fields/parallel.d:40-143) -------------
+// Rank r sends plane nz of every array in `up` to rank r+1's ghost plane 0 and plane 1 of every
+// array in `down` to rank r-1's ghost plane nz+1 (periodic ring), and receives the mirror images.
+// Each plane is one contiguous run of nx*ny elements in the z-slowest SoA layout: no packing.
+// Message order to one peer is [up..., down...] on both sides, so the ring also works when
+// nranks == 2 and both neighbours are the same rank.
+template <typename T>
+int exchange_planes(dlbc_cuda_ctx *ctx, T *base, int64_t array_stride, const std::vector<int> &up,
+                    const std::vector<int> &down, ncclDataType_t dt, cudaStream_t s) {
+  NcclApi &N = nccl_api();
+  const int64_t plane = ctx->g.plane;
+  const int nz = ctx->g.nz;
+  NK(N.GroupStart());
+  for (int a : up) NK(N.Send(base + a * array_stride + (int64_t)nz * plane, (size_t)plane, dt, ctx->up, ctx->nccl, s));
+  for (int a : down) NK(N.Send(base + a * array_stride + plane, (size_t)plane, dt, ctx->down, ctx->nccl, s));
+  for (int a : up) NK(N.Recv(base + a * array_stride, (size_t)plane, dt, ctx->down, ctx->nccl, s));
+  for (int a : down) NK(N.Recv(base + a * array_stride + (int64_t)(nz + 1) * plane, (size_t)plane, dt, ctx->up, ctx->nccl, s));
+  NK(N.GroupEnd());
+  return 0;
+}
+
+void crossing_lists(int ncomp, std::vector<int> &up, std::vector<int> &down) {
+  up.clear();
+  down.clear();
+  for (int c = 0; c < ncomp; c++)
+    for (int q = 0; q < Q; q++) {
+      if (cz(q) == 1) up.push_back(c * Q + q);     // travels to +z: read by the upper neighbour from its ghost 0
+      if (cz(q) == -1) down.push_back(c * Q + q);  // travels to -z
+    }
+}
+
+std::vector<int> iota_list(int n) {
+  std::vector<int> v(n);
+  for (int i = 0; i < n; i++) v[i] = i;
+  return v;
+}
+
+// Make the ghost planes of f[cur] (and the static mask / wall densities) valid.  During time
+// stepping the step kernels / the per-step exchange maintain them; this is the setup path after
+// an upload (the reference's L.exchangeHalo() at main.d:142).
+int ensure_ghosts(dlbc_cuda_ctx *ctx) {
+  const Geom &g = ctx->g;
+  if (!ctx->ghosts_valid) {
+    if (ctx->cfg.nranks == 1) {
+      CK(launch_ghost_fill(g, ctx->f[ctx->cur], (int)pop_arrays(ctx), ctx->compute));
+      ctx->launches++;
+    } else {
+      std::vector<int> up, down;
+      crossing_lists(ctx->cfg.ncomp, up, down);
+      TRY(exchange_planes<double>(ctx, ctx->f[ctx->cur], g.sites_g, up, down, ncclDouble, ctx->compute));
+    }
+    ctx->ghosts_valid = true;
+  }
+  const bool need_wall = ctx->p.any_gwc && ctx->has_solid && ctx->cfg.enable_shan_chen;
+  if (need_wall && !ctx->rho_wall_valid) {
+    if (!ctx->rho_wall) {
+      const size_t bytes = (size_t)ctx->cfg.ncomp * g.sites_g * sizeof(double);
+      CK(cudaMalloc(&ctx->rho_wall, bytes));
+      ctx->device_bytes += (int64_t)bytes;
+    }
+    for (int c = 0; c < ctx->cfg.ncomp; c++) {
+      CK(launch_site_density(g, fcomp(ctx, ctx->cur, c), ctx->rho_wall + (int64_t)c * g.sites_g, ctx->compute));
+      ctx->launches++;
+    }
+    if (ctx->cfg.nranks == 1) {
+      CK(launch_ghost_fill(g, ctx->rho_wall, ctx->cfg.ncomp, ctx->compute));
+      ctx->launches++;
+    } else {
+      const std::vector<int> all = iota_list(ctx->cfg.ncomp);
+      TRY(exchange_planes<double>(ctx, ctx->rho_wall, g.sites_g, all, all, ncclDouble, ctx->compute));
+    }
+    ctx->rho_wall_valid = true;
+  }
+  return 0;
+}
+
+// psi of the current populations' NEXT step input, all planes incl. ghosts (two-pass K1 + exchange)
+int psi_all(dlbc_cuda_ctx *ctx, const StepLaunch &L) {
+  const KernelSet &K = kKernels[ctx->cfg.ncomp - 1];
+  CK(K.psi(L, 1, ctx->g.nz));
+  ctx->launches++;
+  if (ctx->cfg.nranks > 1) {
+    const std::vector<int> all = iota_list(ctx->cfg.ncomp);
+    TRY(exchange_planes<double>(ctx, ctx->psi, ctx->g.sites_g, all, all, ncclDouble, ctx->compute));
+  }
+  return 0;
+}
+
+struct KernelTimer {
+  dlbc_cuda_ctx *ctx;
+  bool on;
+  std::vector<const char *> names;
+  std::vector<cudaEvent_t> evs;
+  cudaEvent_t get(size_t i) {
+    while (ctx->ev_pool.size() <= i) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      ctx->ev_pool.push_back(e);
+    }
+    return ctx->ev_pool[i];
+  }
+  void begin(const char *name) {
+    if (!on) return;
+    cudaEvent_t e = get(evs.size());
+    cudaEventRecord(e, ctx->compute);
+    evs.push_back(e);
+    names.push_back(name);
+  }
+  void end() {
+    if (!on) return;
+    cudaEvent_t e = get(evs.size());
+    cudaEventRecord(e, ctx->compute);
+    evs.push_back(e);
+  }
+};
+
+// One timestep: the statements of runTimeloop, main.d:179-195.
+int step_once(dlbc_cuda_ctx *ctx, KernelTimer *kt) {
+  const KernelSet &K = kKernels[ctx->cfg.ncomp - 1];
+  const int exact = ctx->cfg.arithmetic == DLBC_ARITH_EXACT ? 1 : 0;
+  const int nz = ctx->g.nz;
+  const bool sc = ctx->cfg.enable_shan_chen != 0;
+  const bool zmarch = ctx->variant == DLBC_KERNEL_ZMARCH;
+  StepLaunch L = make_launch(ctx, ctx->compute);
+  launch_fn fused = zmarch ? K.zmarch[exact] : K.fused[exact];
+
+  if (ctx->cfg.nranks == 1) {
+    if (sc && !zmarch) {
+      if (kt) kt->begin("psi_kernel");
+      CK(K.psi(L, 1, nz));
+      ctx->launches++;
+      if (kt) kt->end();
+    }
+    if (kt) kt->begin(zmarch ? "zmarch_kernel" : "fused_kernel");
+    CK(fused(L, 1, nz));
+    ctx->launches++;
+    if (kt) kt->end();
+  } else {
+    // z-slab ring.  compute stream: K1 boundary planes | K1 interior | K2 boundary | K2 interior;
+    // comm stream: psi ghost exchange (overlaps K1 interior), f ghost exchange (overlaps K2
+    // interior).  The reference exchanges 2 full layers of 19 populations per face and per
+    // field, blocking, before every step (fields/parallel.d:70-103).
+    NcclApi &N = nccl_api();
+    (void)N;
+    std::vector<int> up, down;
+    crossing_lists(ctx->cfg.ncomp, up, down);
+    const std::vector<int> all = iota_list(ctx->cfg.ncomp);
+    const int lo = 1, hi = nz;
+    // ghosts of f[cur] were written by the comm stream at the end of the previous step
+    CK(cudaStreamWaitEvent(ctx->compute, ctx->ev_ghost_f, 0));
+    if (sc) {
+      CK(K.psi(L, lo, 1)); ctx->launches++;
+      if (hi != lo) { CK(K.psi(L, hi, 1)); ctx->launches++; }
+      CK(cudaEventRecord(ctx->ev_bnd, ctx->compute));
+      CK(cudaStreamWaitEvent(ctx->comm, ctx->ev_bnd, 0));
+      TRY(exchange_planes<double>(ctx, ctx->psi, ctx->g.sites_g, all, all, ncclDouble, ctx->comm));
+      CK(cudaEventRecord(ctx->ev_ghost_psi, ctx->comm));
+      if (nz > 2) { CK(K.psi(L, lo + 1, nz - 2)); ctx->launches++; }
+      CK(cudaStreamWaitEvent(ctx->compute, ctx->ev_ghost_psi, 0));
+    }
+    CK(K.fused[exact](L, lo, 1)); ctx->launches++;
+    if (hi != lo) { CK(K.fused[exact](L, hi, 1)); ctx->launches++; }
+    CK(cudaEventRecord(ctx->ev_bnd, ctx->compute));
+    CK(cudaStreamWaitEvent(ctx->comm, ctx->ev_bnd, 0));
+    TRY(exchange_planes<double>(ctx, ctx->f[1 - ctx->cur], ctx->g.sites_g, up, down, ncclDouble, ctx->comm));
+    CK(cudaEventRecord(ctx->ev_ghost_f, ctx->comm));
+    if (nz > 2) { CK(K.fused[exact](L, lo + 1, nz - 2)); ctx->launches++; }
+  }
+  ctx->cur ^= 1;
+  ctx->timestep++;
+  ctx->force_valid = true;
+  return 0;
+}
+
+int join_comm(dlbc_cuda_ctx *ctx) {
+  if (ctx->cfg.nranks > 1) CK(cudaStreamWaitEvent(ctx->compute, ctx->ev_ghost_f, 0));
+  return 0;
+}
+
+int check_ctx(dlbc_cuda_ctx *ctx) {
+  if (!ctx) return set_error(nullptr, "dlbc_cuda: null context", 1);
+  cudaError_t e = cudaSetDevice(ctx->device);
+  if (e != cudaSuccess) return cuda_fail(ctx, "cudaSetDevice", e);
+  return 0;
+}
+
+// host <-> staging copies of xc consecutive x-layers of a [..][ny+2h][nz+2h][K] host array.
+// `host_first` addresses the start (y/z halo included) of the first layer moved; the device side
+// is dense and halo-free, [xc][ny][nz][K].
+template <typename T>
+int copy_layers(dlbc_cuda_ctx *ctx, T *host_first, T *dev_dense, int halo, int K, int64_t xc, bool to_device) {
+  const Geom &g = ctx->g;
+  const int64_t NY = g.ny + 2 * halo, NZ = g.nz + 2 * halo;
+  const size_t row = (size_t)g.nz * K * sizeof(T);
+  const cudaMemcpyKind kind = to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
+  if (halo == 0) {
+    if (to_device) CK(cudaMemcpyAsync((void *)dev_dense, (const void *)host_first, row * g.ny * xc, kind, ctx->compute));
+    else CK(cudaMemcpyAsync((void *)host_first, (const void *)dev_dense, row * g.ny * xc, kind, ctx->compute));
+    return 0;
+  }
+  for (int64_t i = 0; i < xc; i++) {
+    T *h = host_first + (i * NY * NZ + (int64_t)halo * NZ + halo) * K;
+    T *d = dev_dense + i * g.ny * g.nz * K;
+    if (to_device) CK(cudaMemcpy2DAsync((void *)d, row, (const void *)h, (size_t)NZ * K * sizeof(T), row, g.ny, kind, ctx->compute));
+    else CK(cudaMemcpy2DAsync((void *)h, (size_t)NZ * K * sizeof(T), (const void *)d, row, row, g.ny, kind, ctx->compute));
+  }
+  return 0;
+}
+
+int64_t chunk_layers(const dlbc_cuda_ctx *ctx, int K, size_t elem) {
+  const int64_t layer = (int64_t)ctx->g.ny * ctx->g.nz * K * (int64_t)elem;
+  int64_t xc = ((int64_t)192 << 20) / std::max<int64_t>(layer, 1);
+  return std::max<int64_t>(1, std::min<int64_t>(xc, ctx->g.nx));
+}
+
+int download_field(dlbc_cuda_ctx *ctx, int kind, int c1, int c2, const double *vec_soa, double *out, int halo) {
+  const Geom &g = ctx->g;
+  const int K = (kind == 2 || kind == 3) ? 3 : 1;
+  const size_t bytes = (size_t)g.nx * g.ny * g.nz * K * sizeof(double);
+  TRY(ensure_stage(ctx, bytes));
+  const double *src = kind == 3 ? vec_soa : ctx->f[ctx->cur];
+  CK(launch_output(g, kind, src, ctx->mask, c1, c2, (double *)ctx->stage, ctx->compute));
+  ctx->launches++;
+  const int64_t NY = g.ny + 2 * halo, NZ = g.nz + 2 * halo;
+  TRY(copy_layers<double>(ctx, out + (int64_t)halo * NY * NZ * K, (double *)ctx->stage, halo, K, g.nx, false));
+  CK(cudaStreamSynchronize(ctx->compute));
+  return release_stage(ctx);
+}
+
+}  // namespace
+
+// =============================================================================================
+extern "C" {
+
+int dlbc_cuda_abi_version(void) { return DLBC_CUDA_ABI_VERSION; }
+
+int dlbc_cuda_device_count(int *count) {
+  dlbc_cuda_ctx *ctx = nullptr;
+  ARG(count, "device_count: null pointer");
+  cudaError_t e = cudaGetDeviceCount(count);
+  if (e != cudaSuccess) {
+    *count = 0;
+    return cuda_fail(nullptr, "cudaGetDeviceCount", e);
+  }
+  return 0;
+}
+
+int dlbc_cuda_nccl_unique_id(uint8_t id[DLBC_CUDA_NCCL_ID_BYTES]) {
+  dlbc_cuda_ctx *ctx = nullptr;
+  static_assert(sizeof(ncclUniqueId) <= DLBC_CUDA_NCCL_ID_BYTES, "ncclUniqueId does not fit");
+  ARG(id, "nccl_unique_id: null pointer");
+  const char *miss = nccl_api().load();
+  if (miss) return set_error(nullptr, miss, 1);
+  ncclUniqueId uid;
+  NK(nccl_api().GetUniqueId(&uid));
+  std::memset(id, 0, DLBC_CUDA_NCCL_ID_BYTES);
+  std::memcpy(id, &uid, sizeof(uid));
+  return 0;
+}
+
+const char *dlbc_cuda_last_error(const dlbc_cuda_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int dlbc_cuda_host_alloc(void **ptr, size_t bytes) {
+  dlbc_cuda_ctx *ctx = nullptr;
+  ARG(ptr, "host_alloc: null pointer");
+  CK(cudaHostAlloc(ptr, bytes, cudaHostAllocDefault));
+  return 0;
+}
+int dlbc_cuda_host_free(void *ptr) {
+  dlbc_cuda_ctx *ctx = nullptr;
+  CK(cudaFreeHost(ptr));
+  return 0;
+}
+
+int dlbc_cuda_destroy(dlbc_cuda_ctx *ctx) {
+  if (!ctx) return 0;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  if (ctx->nccl) nccl_api().CommDestroy(ctx->nccl);
+  for (double *p : {ctx->f[0], ctx->f[1], ctx->psi, ctx->rho_wall, ctx->partial}) if (p) cudaFree(p);
+  if (ctx->mask) cudaFree(ctx->mask);
+  if (ctx->stage) cudaFree(ctx->stage);
+  if (ctx->flags) cudaFree(ctx->flags);
+  for (cudaEvent_t e : {ctx->ev_a, ctx->ev_b, ctx->ev_bnd, ctx->ev_ghost_psi, ctx->ev_ghost_f}) if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
+  for (cudaStream_t s : {ctx->compute, ctx->comm}) if (s) cudaStreamDestroy(s);
+  delete ctx;
+  return 0;
+}
+
+int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
+  dlbc_cuda_ctx *ctx = nullptr;  // errors before the context exists go to the thread-local string
+  ARG(cfg && out, "create: null pointer");
+  *out = nullptr;
+  ARG(cfg->abi_version == DLBC_CUDA_ABI_VERSION, "create: abi_version mismatch");
+  ARG(cfg->d == 3 && cfg->q == 19, "create: only the D3Q19 lattice is built (connectivity.d:21-32)");
+  ARG(cfg->ncomp >= 1 && cfg->ncomp <= DLBC_CUDA_MAX_COMPONENTS, "create: ncomp out of range");
+  ARG(cfg->nranks >= 1 && cfg->rank >= 0 && cfg->rank < cfg->nranks, "create: bad rank/nranks");
+  for (int d = 0; d < 3; d++) ARG(cfg->gn[d] >= 1 && cfg->gn[d] <= 65535, "create: gn out of range (1..65535)");
+  // lattice.d:178,233-241: the global size must be divisible by the process grid
+  ARG(cfg->gn[2] % cfg->nranks == 0, "create: gn[2] is not divisible by nranks (lattice.d:233-241)");
+  ARG(cfg->psi_form == DLBC_PSI_LINEAR || cfg->psi_form == DLBC_PSI_EXPONENTIAL, "create: bad psi_form");
+  ARG(cfg->eqdist_form >= 0 && cfg->eqdist_form <= 2, "create: bad eqdist_form");
+  ARG(cfg->arithmetic == DLBC_ARITH_FAST || cfg->arithmetic == DLBC_ARITH_EXACT, "create: bad arithmetic mode");
+  ARG(cfg->kernel_variant >= DLBC_KERNEL_AUTO && cfg->kernel_variant <= DLBC_KERNEL_ZMARCH, "create: bad kernel_variant");
+  for (int c = 0; c < cfg->ncomp; c++) ARG(cfg->tau[c] > 0.0 && std::isfinite(cfg->tau[c]), "create: tau must be positive");
+
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return set_error(nullptr, std::string("dlbc_cuda_create: no CUDA device (") + cudaGetErrorString(e) +
+                                  "); this library has no CPU fallback", 1000 + (int)e);
+  ARG(cfg->device >= 0 && cfg->device < ndev, "create: device ordinal out of range");
+
+  ctx = new dlbc_cuda_ctx();
+  ctx->cfg = *cfg;
+  ctx->device = cfg->device;
+#define CKC(expr)                                             \
+  do {                                                        \
+    cudaError_t e_ = (expr);                                  \
+    if (e_ != cudaSuccess) {                                  \
+      cuda_fail(ctx, #expr, e_);                              \
+      g_create_error = ctx->err;                              \
+      dlbc_cuda_destroy(ctx);                                 \
+      return 1000 + (int)e_;                                  \
+    }                                                         \
+  } while (0)
+  CKC(cudaSetDevice(ctx->device));
+
+  Geom &g = ctx->g;
+  g.nx = (int)cfg->gn[0];
+  g.ny = (int)cfg->gn[1];
+  g.nz = (int)(cfg->gn[2] / cfg->nranks);
+  g.periodic_z_local = cfg->nranks == 1;
+  g.plane = (int64_t)g.nx * g.ny;
+  g.sites_g = (int64_t)(g.nz + 2) * g.plane;
+
+  StepParams &p = ctx->p;
+  std::memset(&p, 0, sizeof(p));
+  p.ncomp = cfg->ncomp;
+  for (int c = 0; c < cfg->ncomp; c++) {
+    p.tau[c] = cfg->tau[c];
+    p.omega[c] = 1.0 / cfg->tau[c];
+    p.one_minus_omega[c] = 1.0 - p.omega[c];
+    p.inv_tau[c] = p.omega[c];
+    p.tau_pow2[c] = is_pow2(cfg->tau[c]);
+    p.gwc[c] = cfg->gwc[c];
+    if (cfg->gwc[c] != 0.0) p.any_gwc = 1;
+    for (int c2 = 0; c2 < cfg->ncomp; c2++) p.gcc[c * MAXC + c2] = cfg->gcc[c * DLBC_CUDA_MAX_COMPONENTS + c2];
+  }
+  for (int d = 0; d < 3; d++) p.gacc[d] = cfg->global_acc[d];
+
+  ctx->variant = cfg->kernel_variant == DLBC_KERNEL_AUTO ? DLBC_KERNEL_TWO_PASS : cfg->kernel_variant;
+  if (!cfg->enable_shan_chen || cfg->nranks > 1) ctx->variant = DLBC_KERNEL_TWO_PASS;
+#ifndef DLBC_HAVE_ZMARCH
+  ctx->variant = DLBC_KERNEL_TWO_PASS;
+#endif
+
+  CKC(cudaStreamCreateWithFlags(&ctx->compute, cudaStreamNonBlocking));
+  CKC(cudaStreamCreateWithFlags(&ctx->comm, cudaStreamNonBlocking));
+  CKC(cudaEventCreate(&ctx->ev_a));
+  CKC(cudaEventCreate(&ctx->ev_b));
+  CKC(cudaEventCreateWithFlags(&ctx->ev_bnd, cudaEventDisableTiming));
+  CKC(cudaEventCreateWithFlags(&ctx->ev_ghost_psi, cudaEventDisableTiming));
+  CKC(cudaEventCreateWithFlags(&ctx->ev_ghost_f, cudaEventDisableTiming));
+
+  const size_t fbytes = (size_t)cfg->ncomp * Q * g.sites_g * sizeof(double);
+  const size_t sbytes = (size_t)cfg->ncomp * g.sites_g * sizeof(double);
+  CKC(cudaMalloc(&ctx->f[0], fbytes));
+  CKC(cudaMalloc(&ctx->f[1], fbytes));
+  CKC(cudaMalloc(&ctx->psi, sbytes));
+  CKC(cudaMalloc(&ctx->mask, (size_t)g.sites_g));
+  CKC(cudaMalloc(&ctx->partial, (size_t)(4 * REDUCE_BLOCKS + 4) * sizeof(double)));
+  CKC(cudaMalloc(&ctx->flags, 2 * sizeof(int)));
+  ctx->device_bytes = (int64_t)(2 * fbytes + sbytes + g.sites_g + (4 * REDUCE_BLOCKS + 4) * sizeof(double) + 8);
+  CKC(cudaMemsetAsync(ctx->f[0], 0, fbytes, ctx->compute));
+  CKC(cudaMemsetAsync(ctx->f[1], 0, fbytes, ctx->compute));
+  CKC(cudaMemsetAsync(ctx->psi, 0, sbytes, ctx->compute));
+  CKC(cudaMemsetAsync(ctx->mask, 0, (size_t)g.sites_g, ctx->compute));
+  CKC(cudaEventRecord(ctx->ev_ghost_f, ctx->compute));
+  CKC(cudaStreamSynchronize(ctx->compute));
+
+  if (cfg->nranks > 1) {
+    const char *miss = nccl_api().load();
+    if (miss) {
+      g_create_error = miss;
+      dlbc_cuda_destroy(ctx);
+      return 1;
+    }
+    ncclUniqueId uid;
+    std::memcpy(&uid, cfg->nccl_id, sizeof(uid));
+    ncclResult_t r = nccl_api().CommInitRank(&ctx->nccl, cfg->nranks, uid, cfg->rank);
+    if (r != ncclSuccess) {
+      nccl_fail(ctx, "ncclCommInitRank", r);
+      g_create_error = ctx->err;
+      ctx->nccl = nullptr;
+      dlbc_cuda_destroy(ctx);
+      return 2000 + (int)r;
+    }
+    ctx->up = (cfg->rank + 1) % cfg->nranks;
+    ctx->down = (cfg->rank + cfg->nranks - 1) % cfg->nranks;
+  }
+#undef CKC
+  *out = ctx;
+  return 0;
+}
+
+// ---- state transfer -------------------------------------------------------------------------
+int dlbc_cuda_upload_populations_xrange(dlbc_cuda_ctx *ctx, int comp, const double *aos, int halo, int64_t x_begin,
+                                        int64_t x_count) {
+  TRY(check_ctx(ctx));
+  ARG(aos, "upload_populations: null pointer");
+  ARG(comp >= 0 && comp < ctx->cfg.ncomp, "upload_populations: component out of range");
+  ARG(halo >= 0, "upload_populations: negative halo");
+  ARG(x_begin >= 0 && x_count >= 0 && x_begin + x_count <= ctx->g.nx, "upload_populations: x range out of bounds");
+  const Geom &g = ctx->g;
+  TRY(join_comm(ctx));
+  const int64_t xcmax = chunk_layers(ctx, Q, sizeof(double));
+  TRY(ensure_stage(ctx, (size_t)xcmax * g.ny * g.nz * Q * sizeof(double)));
+  // `aos` points at layer x_begin of the host array (the first of the layers moved)
+  const int64_t NY = g.ny + 2 * halo, NZ = g.nz + 2 * halo;
+  for (int64_t x0 = x_begin; x0 < x_begin + x_count; x0 += xcmax) {
+    const int64_t xc = std::min(xcmax, x_begin + x_count - x0);
+    TRY(copy_layers<const double>(ctx, aos + (x0 - x_begin) * NY * NZ * Q, (const double *)ctx->stage, halo, Q, xc, true));
+    CK(launch_aos_to_soa(g, (const double *)ctx->stage, (int)xc, (int)x0, fcomp(ctx, ctx->cur, comp),
+                         fcomp(ctx, 1 - ctx->cur, comp), ctx->compute));
+    ctx->launches++;
+    CK(cudaStreamSynchronize(ctx->compute));  // the staging area is reused by the next chunk
+  }
+  ctx->ghosts_valid = false;
+  ctx->rho_wall_valid = false;
+  ctx->force_valid = false;
+  return 0;
+}
+
+int dlbc_cuda_upload_populations(dlbc_cuda_ctx *ctx, int comp, const double *aos, int halo) {
+  TRY(check_ctx(ctx));
+  ARG(aos, "upload_populations: null pointer");
+  ARG(halo >= 0, "upload_populations: negative halo");
+  // the full-array form receives Field.arr._data.ptr, i.e. the address of layer -halo
+  const int64_t NY = ctx->g.ny + 2 * halo, NZ = ctx->g.nz + 2 * halo;
+  return dlbc_cuda_upload_populations_xrange(ctx, comp, aos + (int64_t)halo * NY * NZ * Q, halo, 0, ctx->g.nx);
+}
+
+int dlbc_cuda_download_populations_xrange(dlbc_cuda_ctx *ctx, int comp, double *aos, int halo, int64_t x_begin,
+                                          int64_t x_count) {
+  TRY(check_ctx(ctx));
+  ARG(aos, "download_populations: null pointer");
+  ARG(comp >= 0 && comp < ctx->cfg.ncomp, "download_populations: component out of range");
+  ARG(halo >= 0, "download_populations: negative halo");
+  ARG(x_begin >= 0 && x_count >= 0 && x_begin + x_count <= ctx->g.nx, "download_populations: x range out of bounds");
+  const Geom &g = ctx->g;
+  TRY(join_comm(ctx));
+  const int64_t xcmax = chunk_layers(ctx, Q, sizeof(double));
+  TRY(ensure_stage(ctx, (size_t)xcmax * g.ny * g.nz * Q * sizeof(double)));
+  const int64_t NY = g.ny + 2 * halo, NZ = g.nz + 2 * halo;
+  for (int64_t x0 = x_begin; x0 < x_begin + x_count; x0 += xcmax) {
+    const int64_t xc = std::min(xcmax, x_begin + x_count - x0);
+    CK(launch_soa_to_aos(g, fcomp(ctx, ctx->cur, comp), (int)xc, (int)x0, (double *)ctx->stage, ctx->compute));
+    ctx->launches++;
+    TRY(copy_layers<double>(ctx, aos + (x0 - x_begin) * NY * NZ * Q, (double *)ctx->stage, halo, Q, xc, false));
+    CK(cudaStreamSynchronize(ctx->compute));
+  }
+  return 0;
+}
+
+int dlbc_cuda_download_populations(dlbc_cuda_ctx *ctx, int comp, double *aos, int halo) {
+  TRY(check_ctx(ctx));
+  ARG(aos, "download_populations: null pointer");
+  ARG(halo >= 0, "download_populations: negative halo");
+  const int64_t NY = ctx->g.ny + 2 * halo, NZ = ctx->g.nz + 2 * halo;
+  return dlbc_cuda_download_populations_xrange(ctx, comp, aos + (int64_t)halo * NY * NZ * Q, halo, 0, ctx->g.nx);
+}
+
+int dlbc_cuda_upload_mask(dlbc_cuda_ctx *ctx, const int32_t *mask, int halo) {
+  TRY(check_ctx(ctx));
+  ARG(mask, "upload_mask: null pointer");
+  ARG(halo >= 0, "upload_mask: negative halo");
+  const Geom &g = ctx->g;
+  TRY(join_comm(ctx));
+  TRY(ensure_stage(ctx, (size_t)g.nx * g.ny * g.nz * sizeof(int32_t)));
+  const int64_t NY = g.ny + 2 * halo, NZ = g.nz + 2 * halo;
+  TRY(copy_layers<const int32_t>(ctx, mask + (int64_t)halo * NY * NZ, (const int32_t *)ctx->stage, halo, 1, g.nx, true));
+  CK(cudaMemsetAsync(ctx->flags, 0, 2 * sizeof(int), ctx->compute));
+  CK(launch_mask_in(g, (const int32_t *)ctx->stage, ctx->mask, ctx->flags, ctx->compute));
+  ctx->launches++;
+  int flags[2] = {0, 0};
+  CK(cudaMemcpyAsync(flags, ctx->flags, sizeof(flags), cudaMemcpyDeviceToHost, ctx->compute));
+  CK(cudaStreamSynchronize(ctx->compute));
+  ARG(flags[0] == 0, "upload_mask: mask values must be 0 (None) or 1 (Solid) (mask.d:84-93)");
+  int solid = flags[1];
+  if (ctx->cfg.nranks == 1) {
+    CK(launch_ghost_fill_mask(g, ctx->mask, ctx->compute));
+    ctx->launches++;
+  } else {
+    const std::vector<int> one = {0};
+    TRY(exchange_planes<uint8_t>(ctx, ctx->mask, g.sites_g, one, one, ncclUint8, ctx->compute));
+    // every rank must take the same kernel path decisions only for itself; but "has_solid" also
+    // has to cover solids in the neighbours' boundary planes (our ghosts): count globally
+    int *dflag = ctx->flags + 1;
+    NK(nccl_api().AllReduce(dflag, dflag, 1, ncclInt32, ncclSum, ctx->nccl, ctx->compute));
+    CK(cudaMemcpyAsync(&solid, dflag, sizeof(int), cudaMemcpyDeviceToHost, ctx->compute));
+  }
+  CK(cudaStreamSynchronize(ctx->compute));
+  ctx->has_solid = solid > 0;
+  ctx->rho_wall_valid = false;
+  ctx->force_valid = false;
+  return release_stage(ctx);
+}
+
+int dlbc_cuda_download_mask(dlbc_cuda_ctx *ctx, int32_t *mask, int halo) {
+  TRY(check_ctx(ctx));
+  ARG(mask, "download_mask: null pointer");
+  ARG(halo >= 0, "download_mask: negative halo");
+  const Geom &g = ctx->g;
+  TRY(ensure_stage(ctx, (size_t)g.nx * g.ny * g.nz * sizeof(int32_t)));
+  CK(launch_mask_out(g, ctx->mask, (int32_t *)ctx->stage, ctx->compute));
+  ctx->launches++;
+  const int64_t NY = g.ny + 2 * halo, NZ = g.nz + 2 * halo;
+  TRY(copy_layers<int32_t>(ctx, mask + (int64_t)halo * NY * NZ, (int32_t *)ctx->stage, halo, 1, g.nx, false));
+  CK(cudaStreamSynchronize(ctx->compute));
+  return release_stage(ctx);
+}
+
+// ---- the hot path ---------------------------------------------------------------------------
+int dlbc_cuda_step(dlbc_cuda_ctx *ctx, int nsteps) {
+  TRY(check_ctx(ctx));
+  ARG(nsteps >= 0, "step: negative step count");
+  if (nsteps == 0) return 0;
+  TRY(ensure_ghosts(ctx));
+  if (ctx->cfg.nranks > 1 && ctx->timestep == 0) CK(cudaEventRecord(ctx->ev_ghost_f, ctx->compute));
+  for (int i = 0; i < nsteps; i++) TRY(step_once(ctx, nullptr));
+  return 0;
+}
+
+int dlbc_cuda_sync(dlbc_cuda_ctx *ctx) {
+  TRY(check_ctx(ctx));
+  CK(cudaStreamSynchronize(ctx->compute));
+  CK(cudaStreamSynchronize(ctx->comm));
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int64_t dlbc_cuda_timestep(const dlbc_cuda_ctx *ctx) { return ctx ? ctx->timestep : -1; }
+
+// ---- outputs --------------------------------------------------------------------------------
+int dlbc_cuda_download_density(dlbc_cuda_ctx *ctx, int comp, double *out, int halo) {
+  TRY(check_ctx(ctx));
+  ARG(out && halo >= 0, "download_density: bad argument");
+  ARG(comp >= 0 && comp < ctx->cfg.ncomp, "download_density: component out of range");
+  TRY(join_comm(ctx));
+  return download_field(ctx, 0, comp, comp, nullptr, out, halo);
+}
+int dlbc_cuda_download_colour(dlbc_cuda_ctx *ctx, int comp1, int comp2, double *out, int halo) {
+  TRY(check_ctx(ctx));
+  ARG(out && halo >= 0, "download_colour: bad argument");
+  ARG(comp1 >= 0 && comp1 < ctx->cfg.ncomp && comp2 >= 0 && comp2 < ctx->cfg.ncomp, "download_colour: component out of range");
+  TRY(join_comm(ctx));
+  return download_field(ctx, 1, comp1, comp2, nullptr, out, halo);
+}
+int dlbc_cuda_download_velocity(dlbc_cuda_ctx *ctx, int comp, double *out, int halo) {
+  TRY(check_ctx(ctx));
+  ARG(out && halo >= 0, "download_velocity: bad argument");
+  ARG(comp >= 0 && comp < ctx->cfg.ncomp, "download_velocity: component out of range");
+  TRY(join_comm(ctx));
+  return download_field(ctx, 2, comp, comp, nullptr, out, halo);
+}
+
+int dlbc_cuda_download_force(dlbc_cuda_ctx *ctx, int comp, double *out, int halo) {
+  TRY(check_ctx(ctx));
+  ARG(out && halo >= 0, "download_force: bad argument");
+  ARG(comp >= 0 && comp < ctx->cfg.ncomp, "download_force: component out of range");
+  const Geom &g = ctx->g;
+  TRY(join_comm(ctx));
+  double *vec = nullptr;
+  const size_t vbytes = (size_t)3 * g.sites_g * sizeof(double);
+  CK(cudaMalloc(&vec, vbytes));
+  int rc = 0;
+  if (!ctx->force_valid || !ctx->cfg.enable_shan_chen) {
+    // before the first step / without Shan-Chen: resetForce leaves zeros (force.d:165-170)
+    cudaMemsetAsync(vec, 0, vbytes, ctx->compute);
+  } else {
+    // recompute psi of the last step's post-advection state from the previous buffer (its ghost
+    // planes are still intact), then the force; the hot path never stores either
+    ctx->cur ^= 1;  // f[cur] := the populations the last step read
+    StepLaunch L = make_launch(ctx, ctx->compute);
+    ctx->cur ^= 1;
+    rc = psi_all(ctx, L);
+    if (!rc) {
+      cudaError_t e = kKernels[ctx->cfg.ncomp - 1].force(L, comp, vec, 1, g.nz);
+      ctx->launches++;
+      if (e != cudaSuccess) rc = cuda_fail(ctx, "force_kernel", e);
+    }
+  }
+  if (!rc) rc = download_field(ctx, 3, comp, comp, vec, out, halo);
+  cudaStreamSynchronize(ctx->compute);
+  cudaFree(vec);
+  return rc;
+}
+
+static int reduce_component(dlbc_cuda_ctx *ctx, int comp, double out4[4]) {
+  const Geom &g = ctx->g;
+  TRY(join_comm(ctx));
+  CK(launch_reduce(g, fcomp(ctx, ctx->cur, comp), ctx->mask, ctx->partial, ctx->compute));
+  ctx->launches += 2;
+  double *res = ctx->partial + 4 * REDUCE_BLOCKS;
+  if (ctx->cfg.nranks > 1) NK(nccl_api().AllReduce(res, res, 4, ncclDouble, ncclSum, ctx->nccl, ctx->compute));
+  CK(cudaMemcpyAsync(out4, res, 4 * sizeof(double), cudaMemcpyDeviceToHost, ctx->compute));
+  CK(cudaStreamSynchronize(ctx->compute));
+  return 0;
+}
+
+int dlbc_cuda_total_mass(dlbc_cuda_ctx *ctx, int comp, double *out) {
+  TRY(check_ctx(ctx));
+  ARG(out, "total_mass: null pointer");
+  ARG(comp >= 0 && comp < ctx->cfg.ncomp, "total_mass: component out of range");
+  double r[4];
+  TRY(reduce_component(ctx, comp, r));
+  *out = r[0];
+  return 0;
+}
+int dlbc_cuda_total_momentum(dlbc_cuda_ctx *ctx, int comp, double out[3]) {
+  TRY(check_ctx(ctx));
+  ARG(out, "total_momentum: null pointer");
+  ARG(comp >= 0 && comp < ctx->cfg.ncomp, "total_momentum: component out of range");
+  double r[4];
+  TRY(reduce_component(ctx, comp, r));
+  out[0] = r[1]; out[1] = r[2]; out[2] = r[3];
+  return 0;
+}
+
+// ---- introspection / measurement ------------------------------------------------------------
+int dlbc_cuda_tables(int64_t *velocities, int64_t *bounce_out, double *weights, double *css) {
+  dlbc_cuda_ctx *ctx = nullptr;
+  ARG(velocities && bounce_out && weights && css, "tables: null pointer");
+  for (int q = 0; q < Q; q++) {
+    velocities[3 * q + 0] = cx(q);
+    velocities[3 * q + 1] = cy(q);
+    velocities[3 * q + 2] = cz(q);
+    bounce_out[q] = bounce(q);
+    weights[q] = weight(q);
+  }
+  *css = 1.0 / 3.0;
+  return 0;
+}
+
+int dlbc_cuda_launch_count(const dlbc_cuda_ctx *ctx, int64_t *count) {
+  if (!ctx || !count) return 1;
+  *count = ctx->launches;
+  return 0;
+}
+
+int dlbc_cuda_device_bytes(const dlbc_cuda_ctx *ctx, int64_t *bytes) {
+  if (!ctx || !bytes) return 1;
+  *bytes = ctx->device_bytes;
+  return 0;
+}
+
+int dlbc_cuda_timed_steps(dlbc_cuda_ctx *ctx, int nsteps, double *elapsed_ms) {
+  TRY(check_ctx(ctx));
+  ARG(nsteps >= 0 && elapsed_ms, "timed_steps: bad argument");
+  TRY(ensure_ghosts(ctx));
+  if (ctx->cfg.nranks > 1 && ctx->timestep == 0) CK(cudaEventRecord(ctx->ev_ghost_f, ctx->compute));
+  TRY(join_comm(ctx));
+  CK(cudaStreamSynchronize(ctx->compute));
+  CK(cudaEventRecord(ctx->ev_a, ctx->compute));
+  for (int i = 0; i < nsteps; i++) TRY(step_once(ctx, nullptr));
+  TRY(join_comm(ctx));
+  CK(cudaEventRecord(ctx->ev_b, ctx->compute));
+  CK(cudaEventSynchronize(ctx->ev_b));
+  float ms = 0.f;
+  CK(cudaEventElapsedTime(&ms, ctx->ev_a, ctx->ev_b));
+  *elapsed_ms = (double)ms;
+  return 0;
+}
+
+int dlbc_cuda_kernel_times(dlbc_cuda_ctx *ctx, int cap, const char **names, double *ms, int *n) {
+  TRY(check_ctx(ctx));
+  ARG(names && ms && n && cap >= 0, "kernel_times: bad argument");
+  ARG(ctx->cfg.nranks == 1, "kernel_times: single-rank contexts only");
+  TRY(ensure_ghosts(ctx));
+  KernelTimer kt{ctx, true, {}, {}};
+  TRY(step_once(ctx, &kt));
+  CK(cudaStreamSynchronize(ctx->compute));
+  *n = 0;
+  for (size_t i = 0; i < kt.names.size() && (int)i < cap; i++) {
+    float t = 0.f;
+    CK(cudaEventElapsedTime(&t, kt.evs[2 * i], kt.evs[2 * i + 1]));
+    names[i] = kt.names[i];
+    ms[i] = (double)t;
+    (*n)++;
+  }
+  return 0;
+}
+
+}  // extern "C"

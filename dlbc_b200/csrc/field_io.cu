@@ -192,9 +192,34 @@ __global__ void output_kernel(Geom g, const double *__restrict__ f, const uint8_
   }
 }
 
+// kind 3: transpose an SoA vector field v[3][zg][y][x] into the dense host order [nx][ny][nz][3]
+__global__ void vector_out_kernel(Geom g, const double *__restrict__ v, double *__restrict__ out) {
+  __shared__ double tile[3][32][33];
+  const int x0 = blockIdx.x * 32, y = blockIdx.y, z0 = blockIdx.z * 32;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int x = x0 + threadIdx.x, z = z0 + j;
+    if (x >= g.nx || z >= g.nz) continue;
+    const int64_t s = ((int64_t)(z + 1) * g.ny + y) * g.nx + x;
+#pragma unroll
+    for (int d = 0; d < 3; d++) tile[d][j][threadIdx.x] = v[(int64_t)d * g.sites_g + s];
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int x = x0 + j, z = z0 + threadIdx.x;
+    if (x >= g.nx || z >= g.nz) continue;
+    const int64_t o = (((int64_t)x * g.ny + y) * g.nz + z) * 3;
+#pragma unroll
+    for (int d = 0; d < 3; d++) out[o + d] = tile[d][threadIdx.x][j];
+  }
+}
+
 cudaError_t launch_output(const Geom &g, int kind, const double *f, const uint8_t *mask, int c1, int c2, double *out,
                           cudaStream_t s) {
   dim3 grid((g.nx + 31) / 32, g.ny, (g.nz + 31) / 32), block(32, 8);
+  if (kind == 3) {
+    vector_out_kernel<<<grid, block, 0, s>>>(g, f, out);
+    return cudaGetLastError();
+  }
   if (kind == 0) output_kernel<0><<<grid, block, 0, s>>>(g, f, mask, c1, c2, out);
   else if (kind == 1) output_kernel<1><<<grid, block, 0, s>>>(g, f, mask, c1, c2, out);
   else if (kind == 2) output_kernel<2><<<grid, block, 0, s>>>(g, f, mask, c1, c2, out);

@@ -9,21 +9,30 @@ struct StepLaunch {
   Geom g;
   Fields f;
   StepParams p;
-  int eq, psi, sc, mask, exact;
+  int eq, psi, sc, mask;
   cudaStream_t stream;
 };
 
 // z_begin / z_count address ghost-inclusive planes: the physical planes are 1..nz.
-// Each returns cudaGetLastError() of its launch.  One function per component count so the
-// heavily unrolled kernels compile in parallel translation units.
+// Each returns cudaGetLastError() of its launch.  One translation unit per (component count,
+// arithmetic mode) so the heavily unrolled kernels compile in parallel and so that the EXACT
+// units can be built with -fmad=false (no FMA contraction: every fp64 operation rounded
+// separately, as the reference's SSE2 code does) while the FAST units keep FMA contraction.
 typedef cudaError_t (*launch_fn)(const StepLaunch &, int z_begin, int z_count);
-cudaError_t launch_psi_c1(const StepLaunch &, int, int);
-cudaError_t launch_psi_c2(const StepLaunch &, int, int);
-cudaError_t launch_psi_c3(const StepLaunch &, int, int);
-cudaError_t launch_psi_c4(const StepLaunch &, int, int);
-cudaError_t launch_fused_c1(const StepLaunch &, int, int);
-cudaError_t launch_fused_c2(const StepLaunch &, int, int);
-cudaError_t launch_fused_c3(const StepLaunch &, int, int);
-cudaError_t launch_fused_c4(const StepLaunch &, int, int);
+// Shan-Chen force of component `comp` (L.force[comp], force.d:238-309) into out[3][sites_g].
+typedef cudaError_t (*force_fn)(const StepLaunch &, int comp, double *out, int z_begin, int z_count);
+
+#define DLBC_DECLARE_STEP(NC)                                                        \
+  cudaError_t launch_psi_c##NC(const StepLaunch &, int, int);                        \
+  cudaError_t launch_force_c##NC(const StepLaunch &, int, double *, int, int);       \
+  cudaError_t launch_fused_exact_c##NC(const StepLaunch &, int, int);                \
+  cudaError_t launch_fused_fast_c##NC(const StepLaunch &, int, int);                 \
+  cudaError_t launch_zmarch_exact_c##NC(const StepLaunch &, int, int);               \
+  cudaError_t launch_zmarch_fast_c##NC(const StepLaunch &, int, int);
+DLBC_DECLARE_STEP(1)
+DLBC_DECLARE_STEP(2)
+DLBC_DECLARE_STEP(3)
+DLBC_DECLARE_STEP(4)
+#undef DLBC_DECLARE_STEP
 
 }  // namespace dlbc

@@ -1,2 +1,3 @@
 #define DLBC_NC 1
+#define DLBC_EXACT 1
 #include "step_cN.inl"

@@ -1,2 +1,3 @@
 #define DLBC_NC 4
+#define DLBC_EXACT 0
 #include "step_cN.inl"

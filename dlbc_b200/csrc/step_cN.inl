@@ -1,4 +1,7 @@
-// step_cN.inl -- instantiates the two-pass kernels for DLBC_NC components (included by step_c*.cu)
+// step_cN.inl -- instantiates the step kernels for DLBC_NC components in arithmetic mode
+// DLBC_EXACT (1: translation unit built with -fmad=false; 0: FMA contraction allowed).
+// Included by step_c<N>_{exact,fast}.cu.  The psi and force kernels (adds, multiplies in
+// reference order, exp) live in the EXACT unit only.
 #include "kernels.h"
 #include "step_two_pass.cuh"
 
@@ -10,8 +13,10 @@ namespace dlbc {
 static inline dim3 block_for(const Geom &g) { return dim3(g.nx >= 128 ? 128 : ((g.nx + 31) / 32) * 32); }
 static inline dim3 grid_for(const Geom &g, dim3 b, int z_count) { return dim3((g.nx + b.x - 1) / b.x, g.ny, z_count); }
 
+#if DLBC_EXACT
 cudaError_t DLBC_CAT(launch_psi_c, DLBC_NC)(const StepLaunch &L, int z_begin, int z_count) {
   constexpr int C = DLBC_NC;
+  if (z_count <= 0) return cudaSuccess;
   const dim3 b = block_for(L.g), gr = grid_for(L.g, b, z_count);
 #define PSI_CASE(PSI, MASK) psi_kernel<C, PSI, MASK><<<gr, b, 0, L.stream>>>(L.g, L.f, z_begin)
   if (L.psi == 0) { if (L.mask) PSI_CASE(0, true); else PSI_CASE(0, false); }
@@ -20,19 +25,30 @@ cudaError_t DLBC_CAT(launch_psi_c, DLBC_NC)(const StepLaunch &L, int z_begin, in
   return cudaGetLastError();
 }
 
+cudaError_t DLBC_CAT(launch_force_c, DLBC_NC)(const StepLaunch &L, int comp, double *out, int z_begin, int z_count) {
+  constexpr int C = DLBC_NC;
+  if (z_count <= 0) return cudaSuccess;
+  const dim3 b = block_for(L.g), gr = grid_for(L.g, b, z_count);
+  if (L.mask) force_kernel<C, true><<<gr, b, 0, L.stream>>>(L.g, L.f, L.p, comp, out, z_begin);
+  else        force_kernel<C, false><<<gr, b, 0, L.stream>>>(L.g, L.f, L.p, comp, out, z_begin);
+  return cudaGetLastError();
+}
+#define DLBC_MODE_NAME(base) DLBC_CAT(DLBC_CAT(base, _exact_c), DLBC_NC)
+constexpr bool kExact = true;
+#else
+#define DLBC_MODE_NAME(base) DLBC_CAT(DLBC_CAT(base, _fast_c), DLBC_NC)
+constexpr bool kExact = false;
+#endif
+
 template <int C, int EQ, bool SC>
 static void fused_dispatch(const StepLaunch &L, dim3 gr, dim3 b, int z_begin) {
-  if (L.mask) {
-    if (L.exact) fused_kernel<C, EQ, SC, true, true><<<gr, b, 0, L.stream>>>(L.g, L.f, L.p, z_begin);
-    else         fused_kernel<C, EQ, SC, true, false><<<gr, b, 0, L.stream>>>(L.g, L.f, L.p, z_begin);
-  } else {
-    if (L.exact) fused_kernel<C, EQ, SC, false, true><<<gr, b, 0, L.stream>>>(L.g, L.f, L.p, z_begin);
-    else         fused_kernel<C, EQ, SC, false, false><<<gr, b, 0, L.stream>>>(L.g, L.f, L.p, z_begin);
-  }
+  if (L.mask) fused_kernel<C, EQ, SC, true, kExact><<<gr, b, 0, L.stream>>>(L.g, L.f, L.p, z_begin);
+  else        fused_kernel<C, EQ, SC, false, kExact><<<gr, b, 0, L.stream>>>(L.g, L.f, L.p, z_begin);
 }
 
-cudaError_t DLBC_CAT(launch_fused_c, DLBC_NC)(const StepLaunch &L, int z_begin, int z_count) {
+cudaError_t DLBC_MODE_NAME(launch_fused)(const StepLaunch &L, int z_begin, int z_count) {
   constexpr int C = DLBC_NC;
+  if (z_count <= 0) return cudaSuccess;
   const dim3 b = block_for(L.g), gr = grid_for(L.g, b, z_count);
   switch (L.eq * 2 + (L.sc ? 1 : 0)) {
     case 0: fused_dispatch<C, 0, false>(L, gr, b, z_begin); break;
@@ -44,6 +60,11 @@ cudaError_t DLBC_CAT(launch_fused_c, DLBC_NC)(const StepLaunch &L, int z_begin, 
     default: return cudaErrorInvalidValue;
   }
   return cudaGetLastError();
+}
+
+// placeholder until step_zmarch.cuh lands: the z-marching variant resolves to the two-pass kernel
+cudaError_t DLBC_MODE_NAME(launch_zmarch)(const StepLaunch &L, int z_begin, int z_count) {
+  return DLBC_MODE_NAME(launch_fused)(L, z_begin, z_count);
 }
 
 }  // namespace dlbc

@@ -165,4 +165,36 @@ __global__ void __launch_bounds__(128) fused_kernel(Geom g, Fields fl, StepParam
   }
 }
 
+// ---- L.force[comp] for output (lb/io.d:86-90) -----------------------------------------------
+// Not on the per-step path: the step kernels keep the force in registers.  Recomputed from the
+// psi field of the last step; zero on solid sites (resetForce, force.d:165-170, and the
+// isCollidable test at force.d:258).
+template <int C, bool MASK>
+__global__ void __launch_bounds__(128) force_kernel(Geom g, Fields fl, StepParams P, int comp,
+                                                    double *__restrict__ out, int z_begin) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= g.nx) return;
+  const int y = blockIdx.y;
+  const int zg = z_begin + blockIdx.z;
+  const Nbr n = make_nbr(g, x, y, zg);
+  const int64_t s = n.at(0, 0, 0);
+  double F[C][3];
+#pragma unroll
+  for (int c = 0; c < C; c++) { F[c][0] = 0.0; F[c][1] = 0.0; F[c][2] = 0.0; }
+  if (!(MASK && fl.mask[s])) {
+    double psi1[C];
+#pragma unroll
+    for (int c = 0; c < C; c++) psi1[c] = fl.psi[(int64_t)c * g.sites_g + s];
+    shan_chen_force<C, MASK>(g, fl, P, n, psi1, F);
+    if (MASK && P.any_gwc) wall_force<C>(g, fl, P, n, psi1, F);
+  }
+#pragma unroll
+  for (int c = 0; c < C; c++) {
+    if (c == comp) {
+#pragma unroll
+      for (int d = 0; d < 3; d++) out[(int64_t)d * g.sites_g + s] = F[c][d];
+    }
+  }
+}
+
 }  // namespace dlbc
