@@ -473,9 +473,7 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
 
   ctx->variant = cfg->kernel_variant == DLBC_KERNEL_AUTO ? DLBC_KERNEL_TWO_PASS : cfg->kernel_variant;
   if (!cfg->enable_shan_chen || cfg->nranks > 1) ctx->variant = DLBC_KERNEL_TWO_PASS;
-#ifndef DLBC_HAVE_ZMARCH
-  ctx->variant = DLBC_KERNEL_TWO_PASS;
-#endif
+  if (cfg->ncomp > 2) ctx->variant = DLBC_KERNEL_TWO_PASS;  // 19 C doubles per thread must stay in registers
 
   CKC(cudaStreamCreateWithFlags(&ctx->compute, cudaStreamNonBlocking));
   CKC(cudaStreamCreateWithFlags(&ctx->comm, cudaStreamNonBlocking));

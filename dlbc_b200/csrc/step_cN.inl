@@ -4,6 +4,8 @@
 // reference order, exp) live in the EXACT unit only.
 #include "kernels.h"
 #include "step_two_pass.cuh"
+#include "step_zmarch.cuh"
+#include <cstdlib>
 
 namespace dlbc {
 
@@ -62,9 +64,57 @@ cudaError_t DLBC_MODE_NAME(launch_fused)(const StepLaunch &L, int z_begin, int z
   return cudaGetLastError();
 }
 
-// placeholder until step_zmarch.cuh lands: the z-marching variant resolves to the two-pass kernel
+// ---- z-marching single-pass variant (Shan-Chen only; C <= 2: 19 C doubles stay in registers) ----
+#if DLBC_NC <= 2
+template <int C, int EQ, int PSI, bool MASK, int TX, int TY, int MINB>
+static cudaError_t zmarch_launch(const StepLaunch &L, int z_begin, int z_count, int chunk) {
+  auto kern = zmarch_kernel<C, EQ, PSI, MASK, kExact, TX, TY, MINB>;
+  constexpr size_t smem = (size_t)(C * Q * TX * TY + 4 * C * (TX + 2) * (TY + 2)) * sizeof(double);
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  ZMarch zm{z_begin, z_begin + z_count, chunk};
+  dim3 grid((L.g.nx + TX - 1) / TX, (L.g.ny + TY - 1) / TY, (z_count + chunk - 1) / chunk);
+  kern<<<grid, dim3(TX, TY), smem, L.stream>>>(L.g, L.f, L.p, zm);
+  return cudaGetLastError();
+}
+
+template <int C, int EQ, int PSI, bool MASK>
+static cudaError_t zmarch_tile(const StepLaunch &L, int z_begin, int z_count) {
+  // tuning knobs (measurement only; defaults are the measured best)
+  static const char *tile = std::getenv("DLBC_ZM_TILE");
+  static const char *ch = std::getenv("DLBC_ZM_CHUNK");
+  int chunk = ch ? std::atoi(ch) : 64;
+  if (chunk < 1) chunk = 64;
+  if (tile && tile[0] == '6' && tile[3] == '4') return zmarch_launch<C, EQ, PSI, MASK, 64, 4, 2>(L, z_begin, z_count, chunk);
+  if (tile && tile[0] == '3') return zmarch_launch<C, EQ, PSI, MASK, 32, 8, 2>(L, z_begin, z_count, chunk);
+  return zmarch_launch<C, EQ, PSI, MASK, 64, 8, 1>(L, z_begin, z_count, chunk);
+}
+
+template <int C, int EQ>
+static cudaError_t zmarch_eq(const StepLaunch &L, int z_begin, int z_count) {
+  if (L.psi == 0) return L.mask ? zmarch_tile<C, EQ, 0, true>(L, z_begin, z_count) : zmarch_tile<C, EQ, 0, false>(L, z_begin, z_count);
+  return L.mask ? zmarch_tile<C, EQ, 1, true>(L, z_begin, z_count) : zmarch_tile<C, EQ, 1, false>(L, z_begin, z_count);
+}
+#endif
+
 cudaError_t DLBC_MODE_NAME(launch_zmarch)(const StepLaunch &L, int z_begin, int z_count) {
-  return DLBC_MODE_NAME(launch_fused)(L, z_begin, z_count);
+  if (z_count <= 0) return cudaSuccess;
+#if DLBC_NC <= 2
+  if (!L.sc) return cudaErrorNotSupported;
+  switch (L.eq) {
+    case 0: return zmarch_eq<DLBC_NC, 0>(L, z_begin, z_count);
+    case 1: return zmarch_eq<DLBC_NC, 1>(L, z_begin, z_count);
+    case 2: return zmarch_eq<DLBC_NC, 2>(L, z_begin, z_count);
+    default: return cudaErrorInvalidValue;
+  }
+#else
+  (void)z_begin;
+  return cudaErrorNotSupported;
+#endif
 }
 
 }  // namespace dlbc

@@ -120,7 +120,7 @@ __device__ __forceinline__ void common_velocity(const StepParams &P, const doubl
 
 // ---- K2 -------------------------------------------------------------------------------------
 template <int C, int EQ, bool SC, bool MASK, bool EXACT>
-__global__ void __launch_bounds__(128) fused_kernel(Geom g, Fields fl, StepParams P, int z_begin) {
+__global__ void __launch_bounds__(128, (MASK && SC) ? 3 : 4) fused_kernel(Geom g, Fields fl, StepParams P, int z_begin) {
   const int x = blockIdx.x * blockDim.x + threadIdx.x;
   if (x >= g.nx) return;
   const int y = blockIdx.y;

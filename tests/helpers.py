@@ -5,10 +5,14 @@ import numpy as np
 RTOL = 1e-12
 
 
-def assert_close(a, b, rtol=RTOL, what=""):
+def assert_close(a, b, rtol=RTOL, what="", scale=None):
+    """`scale`: natural magnitude of the terms the field is summed from, for fields that are small
+    only through cancellation (forces of a near-uniform state, velocities of a fluid at rest)."""
     a, b = np.asarray(a), np.asarray(b)
     assert a.shape == b.shape, (what, a.shape, b.shape)
     s = float(np.max(np.abs(b))) if b.size else 0.0
+    if scale is not None:
+        s = max(s, float(scale))
     bound = rtol * np.maximum(np.abs(b), s)
     err = np.abs(a - b)
     bad = err > bound

@@ -37,6 +37,16 @@ def make_pair(params, pops, mask, **gpu_kw):
     return G, R
 
 
+def compare_force(G, R, nc, gcc, what):
+    """The Shan-Chen force is a sum of 18 * C terms w_q * psi1 * psi2 * g of alternating sign; the 1-ulp
+    freedom of exp() in psi moves each term by ~1e-16 of ITS size, so the tolerance is relative to
+    that term scale (a near-uniform state has |F| ~ 1e-7 from terms ~ 1e-2)."""
+    psimax = max(float(np.max(np.abs(R.psi(c)))) for c in range(nc))
+    term = max(abs(x) for row in gcc for x in row) * psimax * psimax
+    for c in range(nc):
+        assert_close(G.force(c), R.force(c), what=f"{what}: force {c}", scale=term)
+
+
 def compare_state(G, R, nc, what, bitexact=False, steps=1):
     """Populations and densities: 1e-12 relative to the field scale, whatever the step count.
     Velocities are differences of populations (|u| ~ 1e-5 from terms ~ 1e-1), so their round-off
@@ -135,8 +145,8 @@ def test_golden_merging_droplets_3d(golden, kernel):
     assert_close(G.density(1), g["density-blue-t10"], what="t10 blue vs golden")
     assert_close(G.colour(0, 1), g["density-red-t10"] - g["density-blue-t10"], what="t10 colour vs golden")
     compare_state(G, R, 2, "merging droplets t10 vs oracle", steps=10)
+    compare_force(G, R, 2, SC["gcc"], "merging droplets")
     for c in range(2):
-        assert_close(G.force(c), R.force(c), what=f"force {c}")
         assert abs(G.total_mass(c) - m0[c]) / m0[c] < 10 * 1e-14
     G.close()
 
@@ -237,8 +247,8 @@ def test_porous_twin(gwc, kernel):
     R.step(20)
     compare_state(G, R, 2, f"porous gwc={gwc}", steps=20)
     solid = mask == 1
+    compare_force(G, R, 2, SC["gcc"], f"porous gwc={gwc}")
     for c in range(2):
-        assert_close(G.force(c), R.force(c), what=f"force {c}")
         assert_bitexact(G.get_populations(c)[solid], pops[c][solid], "solid sites never change")
         assert (G.velocity(c)[solid] == 0).all() and (G.colour(0, 1)[solid] == 0).all()
         assert abs(G.total_mass(c) - m0[c]) / m0[c] < 20 * 1e-14
@@ -247,9 +257,11 @@ def test_porous_twin(gwc, kernel):
     G.close()
 
 
-@pytest.mark.parametrize("gn", [(7, 5, 3), (33, 2, 1), (130, 3, 2), (1, 1, 1), (16, 16, 40)])
+@pytest.mark.parametrize("gn", [(7, 5, 3), (33, 2, 2), (130, 3, 2), (2, 2, 2), (16, 16, 40)])
 def test_ragged_sizes(gn):
-    """extents that are not multiples of the block/warp size, nz = 1 and 2 (every neighbour wraps)."""
+    """extents that are not multiples of the block/warp size, down to 2 (every neighbour wraps).
+    Extents of 1 are outside the reference's domain: its halo of 2 is filled from the 2 outermost
+    PHYSICAL layers (fields/parallel.d:58-68), which do not exist for n = 1."""
     rng = np.random.default_rng(7)
     mask = (rng.random(gn) < 0.2).astype(np.int32)
     pops = []
@@ -277,8 +289,7 @@ def test_three_components_linear_psi_third_order():
         G.step(10)
         R.step(10)
         compare_state(G, R, 3, f"C=3 linear {arith}", bitexact=(arith == "exact"), steps=10)
-        for c in range(3):
-            assert_close(G.force(c), R.force(c), what=f"force {c}")
+        compare_force(G, R, 3, params["gcc"], f"C=3 {arith}")
         G.close()
 
 
