@@ -193,6 +193,9 @@ def run_ours(args, rank, world, local_rank):
     n = args.size
     ncomp = args.components
     gn = (n, n, n * world)
+    if args.shape:
+        sx, sy, sz = (int(v) for v in args.shape.split(","))
+        gn = (sx, sy, sz * world)
     params = dict(cases.SC2) if ncomp == 2 else dict(tau=[1.0], eqdist_form="SecondOrder", enable_shan_chen=False)
     G = Lattice(gn, ncomp, **params, arithmetic=args.arith, kernel=args.kernel, device=local_rank,
                 rank=rank, nranks=world, nccl_id=nccl_id)
@@ -328,6 +331,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--size", type=int, default=512, help="lattice edge per GPU")
+    ap.add_argument("--shape", default=None, help="nx,ny,nz per GPU (overrides --size; profiling runs)")
     ap.add_argument("--components", type=int, default=2)
     ap.add_argument("--arith", default="fast", choices=["fast", "exact"])
     ap.add_argument("--kernel", default="auto", choices=["auto", "two_pass", "zmarch"])

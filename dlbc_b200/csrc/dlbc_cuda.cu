@@ -72,8 +72,6 @@ bool is_pow2(double x) {
   return x > 0.0 && std::frexp(x, &e) == 0.5;
 }
 
-int64_t pop_arrays(const dlbc_cuda_ctx *ctx) { return (int64_t)ctx->cfg.ncomp * Q; }
-double *fcomp(dlbc_cuda_ctx *ctx, int buf, int comp) { return ctx->f[buf] + (int64_t)comp * Q * ctx->g.sites_g; }
 
 int ensure_stage(dlbc_cuda_ctx *ctx, size_t bytes) {
   if (bytes <= ctx->stage_bytes) return 0;
@@ -120,40 +118,62 @@ StepLaunch make_launch(dlbc_cuda_ctx *ctx, cudaStream_t s) {
 }
 
 // ---- NCCL ghost-plane exchange: replaces exchangeHalo (fields/parallel.d:40-143) -------------
-// Rank r sends plane nz of every array in `up` to rank r+1's ghost plane 0 and plane 1 of every
-// array in `down` to rank r-1's ghost plane nz+1 (periodic ring), and receives the mirror images.
-// Each plane is one contiguous run of nx*ny elements in the z-slowest SoA layout: no packing.
-// Message order to one peer is [up..., down...] on both sides, so the ring also works when
-// nranks == 2 and both neighbours are the same rank.
+// Rank r sends its plane nz of every array in the "up" list to rank r+1's ghost plane 0 and its
+// plane 1 of every array in the "down" list to rank r-1's ghost plane nz+1 (periodic ring), and
+// receives the mirror images.  Each plane of one array is one contiguous run of nx*ny elements in
+// both device layouts: no packing.  Message order to one peer is [up..., down...] on both sides,
+// so the ring also works when nranks == 2 and both neighbours are the same rank.
 template <typename T>
-int exchange_planes(dlbc_cuda_ctx *ctx, T *base, int64_t array_stride, const std::vector<int> &up,
-                    const std::vector<int> &down, ncclDataType_t dt, cudaStream_t s) {
+struct PlaneXfer {
+  std::vector<T *> send_up, recv_from_down;   // my plane nz   -> upper neighbour's ghost 0
+  std::vector<T *> send_down, recv_from_up;   // my plane 1    -> lower neighbour's ghost nz+1
+};
+
+template <typename T>
+int exchange_planes(dlbc_cuda_ctx *ctx, const PlaneXfer<T> &x, ncclDataType_t dt, cudaStream_t s) {
   NcclApi &N = nccl_api();
-  const int64_t plane = ctx->g.plane;
-  const int nz = ctx->g.nz;
+  const size_t plane = (size_t)ctx->g.plane;
   NK(N.GroupStart());
-  for (int a : up) NK(N.Send(base + a * array_stride + (int64_t)nz * plane, (size_t)plane, dt, ctx->up, ctx->nccl, s));
-  for (int a : down) NK(N.Send(base + a * array_stride + plane, (size_t)plane, dt, ctx->down, ctx->nccl, s));
-  for (int a : up) NK(N.Recv(base + a * array_stride, (size_t)plane, dt, ctx->down, ctx->nccl, s));
-  for (int a : down) NK(N.Recv(base + a * array_stride + (int64_t)(nz + 1) * plane, (size_t)plane, dt, ctx->up, ctx->nccl, s));
+  for (T *p : x.send_up) NK(N.Send(p, plane, dt, ctx->up, ctx->nccl, s));
+  for (T *p : x.send_down) NK(N.Send(p, plane, dt, ctx->down, ctx->nccl, s));
+  for (T *p : x.recv_from_down) NK(N.Recv(p, plane, dt, ctx->down, ctx->nccl, s));
+  for (T *p : x.recv_from_up) NK(N.Recv(p, plane, dt, ctx->up, ctx->nccl, s));
   NK(N.GroupEnd());
   return 0;
 }
 
-void crossing_lists(int ncomp, std::vector<int> &up, std::vector<int> &down) {
-  up.clear();
-  down.clear();
-  for (int c = 0; c < ncomp; c++)
-    for (int q = 0; q < Q; q++) {
-      if (cz(q) == 1) up.push_back(c * Q + q);     // travels to +z: read by the upper neighbour from its ghost 0
-      if (cz(q) == -1) down.push_back(c * Q + q);  // travels to -z
-    }
+// fields laid out [narrays][zg][y][x] (psi, wall densities, mask): all arrays go both ways
+template <typename T>
+PlaneXfer<T> scalar_xfer(const dlbc_cuda_ctx *ctx, T *base, int narrays) {
+  PlaneXfer<T> x;
+  const Geom &g = ctx->g;
+  for (int a = 0; a < narrays; a++) {
+    T *p = base + (int64_t)a * g.sites_g;
+    x.send_up.push_back(p + (int64_t)g.nz * g.plane);
+    x.recv_from_down.push_back(p);
+    x.send_down.push_back(p + g.plane);
+    x.recv_from_up.push_back(p + (int64_t)(g.nz + 1) * g.plane);
+  }
+  return x;
 }
 
-std::vector<int> iota_list(int n) {
-  std::vector<int> v(n);
-  for (int i = 0; i < n; i++) v[i] = i;
-  return v;
+// populations f[zg][c][q][y][x]: only the five directions per component that cross each face
+// (+z: q in {5,9,10,11,17}; -z: q in {6,12,15,16,18}; connectivity.d:401-418).  The reference
+// ships 2 full layers x 19 populations per face instead (fields/parallel.d:58-68).
+PlaneXfer<double> population_xfer(const dlbc_cuda_ctx *ctx, double *f) {
+  PlaneXfer<double> x;
+  const Geom &g = ctx->g;
+  for (int c = 0; c < ctx->cfg.ncomp; c++)
+    for (int q = 0; q < Q; q++) {
+      if (cz(q) == 1) {
+        x.send_up.push_back(f + f_index(g, c, q, g.nz, 0));
+        x.recv_from_down.push_back(f + f_index(g, c, q, 0, 0));
+      } else if (cz(q) == -1) {
+        x.send_down.push_back(f + f_index(g, c, q, 1, 0));
+        x.recv_from_up.push_back(f + f_index(g, c, q, g.nz + 1, 0));
+      }
+    }
+  return x;
 }
 
 // Make the ghost planes of f[cur] (and the static mask / wall densities) valid.  During time
@@ -162,13 +182,14 @@ std::vector<int> iota_list(int n) {
 int ensure_ghosts(dlbc_cuda_ctx *ctx) {
   const Geom &g = ctx->g;
   if (!ctx->ghosts_valid) {
+    double *f = ctx->f[ctx->cur];
     if (ctx->cfg.nranks == 1) {
-      CK(launch_ghost_fill(g, ctx->f[ctx->cur], (int)pop_arrays(ctx), ctx->compute));
-      ctx->launches++;
+      // a whole plane of all C*19 arrays is one contiguous block
+      const size_t bytes = (size_t)g.fz * sizeof(double);
+      CK(cudaMemcpyAsync(f, f + (int64_t)g.nz * g.fz, bytes, cudaMemcpyDeviceToDevice, ctx->compute));
+      CK(cudaMemcpyAsync(f + (int64_t)(g.nz + 1) * g.fz, f + g.fz, bytes, cudaMemcpyDeviceToDevice, ctx->compute));
     } else {
-      std::vector<int> up, down;
-      crossing_lists(ctx->cfg.ncomp, up, down);
-      TRY(exchange_planes<double>(ctx, ctx->f[ctx->cur], g.sites_g, up, down, ncclDouble, ctx->compute));
+      TRY(exchange_planes<double>(ctx, population_xfer(ctx, f), ncclDouble, ctx->compute));
     }
     ctx->ghosts_valid = true;
   }
@@ -180,15 +201,14 @@ int ensure_ghosts(dlbc_cuda_ctx *ctx) {
       ctx->device_bytes += (int64_t)bytes;
     }
     for (int c = 0; c < ctx->cfg.ncomp; c++) {
-      CK(launch_site_density(g, fcomp(ctx, ctx->cur, c), ctx->rho_wall + (int64_t)c * g.sites_g, ctx->compute));
+      CK(launch_site_density(g, ctx->f[ctx->cur], c, ctx->rho_wall + (int64_t)c * g.sites_g, ctx->compute));
       ctx->launches++;
     }
     if (ctx->cfg.nranks == 1) {
       CK(launch_ghost_fill(g, ctx->rho_wall, ctx->cfg.ncomp, ctx->compute));
       ctx->launches++;
     } else {
-      const std::vector<int> all = iota_list(ctx->cfg.ncomp);
-      TRY(exchange_planes<double>(ctx, ctx->rho_wall, g.sites_g, all, all, ncclDouble, ctx->compute));
+      TRY(exchange_planes<double>(ctx, scalar_xfer(ctx, ctx->rho_wall, ctx->cfg.ncomp), ncclDouble, ctx->compute));
     }
     ctx->rho_wall_valid = true;
   }
@@ -201,8 +221,7 @@ int psi_all(dlbc_cuda_ctx *ctx, const StepLaunch &L) {
   CK(K.psi(L, 1, ctx->g.nz));
   ctx->launches++;
   if (ctx->cfg.nranks > 1) {
-    const std::vector<int> all = iota_list(ctx->cfg.ncomp);
-    TRY(exchange_planes<double>(ctx, ctx->psi, ctx->g.sites_g, all, all, ncclDouble, ctx->compute));
+    TRY(exchange_planes<double>(ctx, scalar_xfer(ctx, ctx->psi, ctx->cfg.ncomp), ncclDouble, ctx->compute));
   }
   return 0;
 }
@@ -261,11 +280,6 @@ int step_once(dlbc_cuda_ctx *ctx, KernelTimer *kt) {
     // comm stream: psi ghost exchange (overlaps K1 interior), f ghost exchange (overlaps K2
     // interior).  The reference exchanges 2 full layers of 19 populations per face and per
     // field, blocking, before every step (fields/parallel.d:70-103).
-    NcclApi &N = nccl_api();
-    (void)N;
-    std::vector<int> up, down;
-    crossing_lists(ctx->cfg.ncomp, up, down);
-    const std::vector<int> all = iota_list(ctx->cfg.ncomp);
     const int lo = 1, hi = nz;
     // ghosts of f[cur] were written by the comm stream at the end of the previous step
     CK(cudaStreamWaitEvent(ctx->compute, ctx->ev_ghost_f, 0));
@@ -274,7 +288,7 @@ int step_once(dlbc_cuda_ctx *ctx, KernelTimer *kt) {
       if (hi != lo) { CK(K.psi(L, hi, 1)); ctx->launches++; }
       CK(cudaEventRecord(ctx->ev_bnd, ctx->compute));
       CK(cudaStreamWaitEvent(ctx->comm, ctx->ev_bnd, 0));
-      TRY(exchange_planes<double>(ctx, ctx->psi, ctx->g.sites_g, all, all, ncclDouble, ctx->comm));
+      TRY(exchange_planes<double>(ctx, scalar_xfer(ctx, ctx->psi, ctx->cfg.ncomp), ncclDouble, ctx->comm));
       CK(cudaEventRecord(ctx->ev_ghost_psi, ctx->comm));
       if (nz > 2) { CK(K.psi(L, lo + 1, nz - 2)); ctx->launches++; }
       CK(cudaStreamWaitEvent(ctx->compute, ctx->ev_ghost_psi, 0));
@@ -283,7 +297,7 @@ int step_once(dlbc_cuda_ctx *ctx, KernelTimer *kt) {
     if (hi != lo) { CK(K.fused[exact](L, hi, 1)); ctx->launches++; }
     CK(cudaEventRecord(ctx->ev_bnd, ctx->compute));
     CK(cudaStreamWaitEvent(ctx->comm, ctx->ev_bnd, 0));
-    TRY(exchange_planes<double>(ctx, ctx->f[1 - ctx->cur], ctx->g.sites_g, up, down, ncclDouble, ctx->comm));
+    TRY(exchange_planes<double>(ctx, population_xfer(ctx, ctx->f[1 - ctx->cur]), ncclDouble, ctx->comm));
     CK(cudaEventRecord(ctx->ev_ghost_f, ctx->comm));
     if (nz > 2) { CK(K.fused[exact](L, lo + 1, nz - 2)); ctx->launches++; }
   }
@@ -453,7 +467,16 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
   g.ny = (int)cfg->gn[1];
   g.nz = (int)(cfg->gn[2] / cfg->nranks);
   g.periodic_z_local = cfg->nranks == 1;
-  g.plane = (int64_t)g.nx * g.ny;
+  // per-thread addressing is 32-bit offsets within three consecutive plane blocks (lattice.cuh)
+  if ((int64_t)g.nx * g.ny * cfg->ncomp * Q * 3 >= ((int64_t)1 << 31)) {
+    g_create_error = "dlbc_cuda: create: nx*ny*ncomp*57 must be below 2^31 (32-bit in-plane addressing)";
+    dlbc_cuda_destroy(ctx);
+    return 1;
+  }
+  g.plane = g.nx * g.ny;
+  g.fc = Q * g.plane;
+  g.fz = cfg->ncomp * Q * g.plane;
+  g.ncomp = cfg->ncomp;
   g.sites_g = (int64_t)(g.nz + 2) * g.plane;
 
   StepParams &p = ctx->p;
@@ -541,8 +564,8 @@ int dlbc_cuda_upload_populations_xrange(dlbc_cuda_ctx *ctx, int comp, const doub
   for (int64_t x0 = x_begin; x0 < x_begin + x_count; x0 += xcmax) {
     const int64_t xc = std::min(xcmax, x_begin + x_count - x0);
     TRY(copy_layers<const double>(ctx, aos + (x0 - x_begin) * NY * NZ * Q, (const double *)ctx->stage, halo, Q, xc, true));
-    CK(launch_aos_to_soa(g, (const double *)ctx->stage, (int)xc, (int)x0, fcomp(ctx, ctx->cur, comp),
-                         fcomp(ctx, 1 - ctx->cur, comp), ctx->compute));
+    CK(launch_aos_to_soa(g, (const double *)ctx->stage, (int)xc, (int)x0, comp, ctx->f[ctx->cur], ctx->f[1 - ctx->cur],
+                         ctx->compute));
     ctx->launches++;
     CK(cudaStreamSynchronize(ctx->compute));  // the staging area is reused by the next chunk
   }
@@ -575,7 +598,7 @@ int dlbc_cuda_download_populations_xrange(dlbc_cuda_ctx *ctx, int comp, double *
   const int64_t NY = g.ny + 2 * halo, NZ = g.nz + 2 * halo;
   for (int64_t x0 = x_begin; x0 < x_begin + x_count; x0 += xcmax) {
     const int64_t xc = std::min(xcmax, x_begin + x_count - x0);
-    CK(launch_soa_to_aos(g, fcomp(ctx, ctx->cur, comp), (int)xc, (int)x0, (double *)ctx->stage, ctx->compute));
+    CK(launch_soa_to_aos(g, ctx->f[ctx->cur], (int)xc, (int)x0, comp, (double *)ctx->stage, ctx->compute));
     ctx->launches++;
     TRY(copy_layers<double>(ctx, aos + (x0 - x_begin) * NY * NZ * Q, (double *)ctx->stage, halo, Q, xc, false));
     CK(cudaStreamSynchronize(ctx->compute));
@@ -612,8 +635,7 @@ int dlbc_cuda_upload_mask(dlbc_cuda_ctx *ctx, const int32_t *mask, int halo) {
     CK(launch_ghost_fill_mask(g, ctx->mask, ctx->compute));
     ctx->launches++;
   } else {
-    const std::vector<int> one = {0};
-    TRY(exchange_planes<uint8_t>(ctx, ctx->mask, g.sites_g, one, one, ncclUint8, ctx->compute));
+    TRY(exchange_planes<uint8_t>(ctx, scalar_xfer(ctx, ctx->mask, 1), ncclUint8, ctx->compute));
     // every rank must take the same kernel path decisions only for itself; but "has_solid" also
     // has to cover solids in the neighbours' boundary planes (our ghosts): count globally
     int *dflag = ctx->flags + 1;
@@ -720,7 +742,7 @@ int dlbc_cuda_download_force(dlbc_cuda_ctx *ctx, int comp, double *out, int halo
 static int reduce_component(dlbc_cuda_ctx *ctx, int comp, double out4[4]) {
   const Geom &g = ctx->g;
   TRY(join_comm(ctx));
-  CK(launch_reduce(g, fcomp(ctx, ctx->cur, comp), ctx->mask, ctx->partial, ctx->compute));
+  CK(launch_reduce(g, ctx->f[ctx->cur], comp, ctx->mask, ctx->partial, ctx->compute));
   ctx->launches += 2;
   double *res = ctx->partial + 4 * REDUCE_BLOCKS;
   if (ctx->cfg.nranks > 1) NK(nccl_api().AllReduce(res, res, 4, ncclDouble, ncclSum, ctx->nccl, ctx->compute));

@@ -1,5 +1,5 @@
 // field_io.cu -- layout conversion between the reference's host arrays (AoS f[x][y][z][q], z
-// fastest, src/dlbc/fields/field.d:114-125) and the device's SoA f[q][zg][y][x] (x fastest),
+// fastest, src/dlbc/fields/field.d:114-125) and the device's SoA f[zg][c][q][y][x] (x fastest),
 // derived output fields (lb/io.d:56-101) and global reductions (density.d:136-180,
 // momentum.d:129-180).  None of this is on the per-step hot path.
 #include "field_io.h"
@@ -8,11 +8,11 @@ namespace dlbc {
 
 constexpr int TILE = 16;
 
-// ---- populations: dense AoS chunk [xc][ny][nz][19]  <->  SoA [q][zg][y][x0 + xi] ------------
+// ---- populations: dense AoS chunk [xc][ny][nz][19]  <->  SoA [zg][c][q][y][x0 + xi] ---------
 // One block per (z-tile, y, x-tile): reads are contiguous runs of TILE*19 doubles per x-layer,
 // writes are contiguous runs of TILE doubles along x; the transposition goes through shared
 // memory (row pitch TILE*19+1 doubles: odd, so the strided phase is bank-conflict free).
-__global__ void __launch_bounds__(256) aos_to_soa_kernel(Geom g, const double *__restrict__ aos, int xc, int x0,
+__global__ void __launch_bounds__(256) aos_to_soa_kernel(Geom g, const double *__restrict__ aos, int xc, int x0, int c,
                                                          double *__restrict__ soa_a, double *__restrict__ soa_b) {
   __shared__ double tile[TILE][TILE * Q + 1];
   const int z0 = blockIdx.x * TILE, y = blockIdx.y, xi0 = blockIdx.z * TILE;
@@ -27,14 +27,14 @@ __global__ void __launch_bounds__(256) aos_to_soa_kernel(Geom g, const double *_
     const int xi = i % TILE, zq = i / TILE;
     if (xi >= nxt) continue;
     const int zz = zq / Q, q = zq % Q;
-    const int64_t dst = (int64_t)q * g.sites_g + ((int64_t)(z0 + zz + 1) * g.ny + y) * g.nx + x0 + xi0 + xi;
+    const int64_t dst = f_index(g, c, q, z0 + zz + 1, (int64_t)y * g.nx + x0 + xi0 + xi);
     const double v = tile[xi][zz * Q + q];
     soa_a[dst] = v;
     if (soa_b) soa_b[dst] = v;
   }
 }
 
-__global__ void __launch_bounds__(256) soa_to_aos_kernel(Geom g, const double *__restrict__ soa, int xc, int x0,
+__global__ void __launch_bounds__(256) soa_to_aos_kernel(Geom g, const double *__restrict__ soa, int xc, int x0, int c,
                                                          double *__restrict__ aos) {
   __shared__ double tile[TILE][TILE * Q + 1];
   const int z0 = blockIdx.x * TILE, y = blockIdx.y, xi0 = blockIdx.z * TILE;
@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(256) soa_to_aos_kernel(Geom g, const double *_
     const int xi = i % TILE, zq = i / TILE;
     if (xi >= nxt) continue;
     const int zz = zq / Q, q = zq % Q;
-    tile[xi][zz * Q + q] = soa[(int64_t)q * g.sites_g + ((int64_t)(z0 + zz + 1) * g.ny + y) * g.nx + x0 + xi0 + xi];
+    tile[xi][zz * Q + q] = soa[f_index(g, c, q, z0 + zz + 1, (int64_t)y * g.nx + x0 + xi0 + xi)];
   }
   __syncthreads();
   for (int xi = 0; xi < nxt; xi++) {
@@ -53,16 +53,16 @@ __global__ void __launch_bounds__(256) soa_to_aos_kernel(Geom g, const double *_
   }
 }
 
-cudaError_t launch_aos_to_soa(const Geom &g, const double *aos, int xc, int x0, double *soa_a, double *soa_b,
+cudaError_t launch_aos_to_soa(const Geom &g, const double *aos, int xc, int x0, int c, double *soa_a, double *soa_b,
                               cudaStream_t s) {
   dim3 grid((g.nz + TILE - 1) / TILE, g.ny, (xc + TILE - 1) / TILE);
-  aos_to_soa_kernel<<<grid, 256, 0, s>>>(g, aos, xc, x0, soa_a, soa_b);
+  aos_to_soa_kernel<<<grid, 256, 0, s>>>(g, aos, xc, x0, c, soa_a, soa_b);
   return cudaGetLastError();
 }
 
-cudaError_t launch_soa_to_aos(const Geom &g, const double *soa, int xc, int x0, double *aos, cudaStream_t s) {
+cudaError_t launch_soa_to_aos(const Geom &g, const double *soa, int xc, int x0, int c, double *aos, cudaStream_t s) {
   dim3 grid((g.nz + TILE - 1) / TILE, g.ny, (xc + TILE - 1) / TILE);
-  soa_to_aos_kernel<<<grid, 256, 0, s>>>(g, soa, xc, x0, aos);
+  soa_to_aos_kernel<<<grid, 256, 0, s>>>(g, soa, xc, x0, c, aos);
   return cudaGetLastError();
 }
 
@@ -116,9 +116,8 @@ cudaError_t launch_mask_out(const Geom &g, const uint8_t *in, int32_t *out, cuda
 }
 
 // ---- ghost planes when the slab is its own z neighbour ---------------------------------------
-// Populations: only the five directions that cross each face are ever read from a ghost plane
-// (pull of q with c_z = +1 reads zg - 1; c_z = -1 reads zg + 1).  We copy all 19 for simplicity
-// here (setup path); the step kernels maintain just the five during time stepping.
+// For fields laid out [narrays][zg][y][x] (psi, wall densities).  The populations' ghost planes
+// are whole contiguous plane blocks in the plane-major layout and are copied with cudaMemcpyAsync.
 __global__ void ghost_fill_kernel(Geom g, double *__restrict__ f, int narrays) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= g.plane) return;
@@ -150,9 +149,11 @@ cudaError_t launch_ghost_fill_mask(const Geom &g, uint8_t *m, cudaStream_t s) {
 // kind 2: raw velocity of c1 (rawVelocityField, velocity.d:106-117: zero on solid sites)
 // kind 3: own-site density into an SoA array (no transposition) for rho_wall
 // Output (kinds 0-2): dense [nx][ny][nz][K] (K = 1 or 3), written through a 32x32 (x,z) tile.
-__device__ __forceinline__ void load_site(const double *__restrict__ fc, int64_t qstride, int64_t s, double (&f)[Q]) {
+__device__ __forceinline__ void load_site(const double *__restrict__ f, const Geom &g, int c, int zg, int sxy,
+                                          double (&v)[Q]) {
+  const double *__restrict__ p = f_plane(f, g, zg, c) + sxy;
 #pragma unroll
-  for (int q = 0; q < Q; q++) f[q] = fc[(int64_t)q * qstride + s];
+  for (int q = 0; q < Q; q++) v[q] = p[q * g.plane];
 }
 
 template <int KIND>
@@ -167,12 +168,12 @@ __global__ void output_kernel(Geom g, const double *__restrict__ f, const uint8_
     const int64_t s = ((int64_t)(z + 1) * g.ny + y) * g.nx + x;
     const bool fluid = mask[s] == 0;
     double fa[Q];
-    load_site(f + (int64_t)c1 * Q * g.sites_g, g.sites_g, s, fa);
+    load_site(f, g, c1, z + 1, y * g.nx + x, fa);
     if (KIND == 0) {
       tile[0][j][threadIdx.x] = density19(fa);
     } else if (KIND == 1) {
       double fb[Q];
-      load_site(f + (int64_t)c2 * Q * g.sites_g, g.sites_g, s, fb);
+      load_site(f, g, c2, z + 1, y * g.nx + x, fb);
       tile[0][j][threadIdx.x] = fluid ? density19(fa) - density19(fb) : 0.0;
     } else {
       double m[3];
@@ -229,15 +230,15 @@ cudaError_t launch_output(const Geom &g, int kind, const double *f, const uint8_
 
 // Own-site densities of every site incl. ghosts, SoA (for the wall term, force.d:298: the density
 // "on the wall" is the sum of the solid site's own, never-advected populations).
-__global__ void site_density_kernel(Geom g, const double *__restrict__ fc, double *__restrict__ rho) {
+__global__ void site_density_kernel(Geom g, const double *__restrict__ f, int c, double *__restrict__ rho) {
   const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= g.sites_g) return;
-  double f[Q];
-  load_site(fc, g.sites_g, s, f);
-  rho[s] = density19(f);
+  double v[Q];
+  load_site(f, g, c, (int)(s / g.plane), (int)(s % g.plane), v);
+  rho[s] = density19(v);
 }
-cudaError_t launch_site_density(const Geom &g, const double *fc, double *rho, cudaStream_t s) {
-  site_density_kernel<<<(unsigned)((g.sites_g + 255) / 256), 256, 0, s>>>(g, fc, rho);
+cudaError_t launch_site_density(const Geom &g, const double *f, int c, double *rho, cudaStream_t s) {
+  site_density_kernel<<<(unsigned)((g.sites_g + 255) / 256), 256, 0, s>>>(g, f, c, rho);
   return cudaGetLastError();
 }
 
@@ -258,7 +259,7 @@ __device__ __forceinline__ double block_sum(double v, double *sh) {
   return r;
 }
 
-__global__ void __launch_bounds__(256) reduce_sites_kernel(Geom g, const double *__restrict__ fc,
+__global__ void __launch_bounds__(256) reduce_sites_kernel(Geom g, const double *__restrict__ fp, int c,
                                                            const uint8_t *__restrict__ mask, double *__restrict__ partial) {
   __shared__ double sh[8];
   double acc[4] = {0.0, 0.0, 0.0, 0.0};
@@ -267,7 +268,7 @@ __global__ void __launch_bounds__(256) reduce_sites_kernel(Geom g, const double 
     const int64_t s = i + g.plane;  // skip ghost plane 0
     if (mask[s]) continue;          // isFluid only (density.d:142, momentum.d:135)
     double f[Q], m[3];
-    load_site(fc, g.sites_g, s, f);
+    load_site(fp, g, c, (int)(s / g.plane), (int)(s % g.plane), f);
     momentum19(f, m);
     acc[0] += density19(f);
     acc[1] += m[0]; acc[2] += m[1]; acc[3] += m[2];
@@ -288,8 +289,8 @@ __global__ void __launch_bounds__(256) reduce_final_kernel(double *__restrict__ 
   }
 }
 
-cudaError_t launch_reduce(const Geom &g, const double *fc, const uint8_t *mask, double *partial, cudaStream_t s) {
-  reduce_sites_kernel<<<REDUCE_BLOCKS, 256, 0, s>>>(g, fc, mask, partial);
+cudaError_t launch_reduce(const Geom &g, const double *f, int c, const uint8_t *mask, double *partial, cudaStream_t s) {
+  reduce_sites_kernel<<<REDUCE_BLOCKS, 256, 0, s>>>(g, f, c, mask, partial);
   reduce_final_kernel<<<1, 256, 0, s>>>(partial);
   return cudaGetLastError();
 }

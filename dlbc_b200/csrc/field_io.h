@@ -11,15 +11,16 @@ constexpr int REDUCE_BLOCKS = 1184;  // 8 per SM on a 148-SM B200; fixed so redu
 
 // Staged device arrays are dense and halo-free (the halo of the host's Field.arr is stripped or
 // skipped by the strided host<->device copy): `aos` = [xc][ny][nz][19] for x-layers x0..x0+xc.
-cudaError_t launch_aos_to_soa(const Geom &g, const double *aos, int xc, int x0, double *soa_a, double *soa_b,
+// soa_a / soa_b / soa: the whole population buffer f[zg][c][q][y][x]; c selects the component.
+cudaError_t launch_aos_to_soa(const Geom &g, const double *aos, int xc, int x0, int c, double *soa_a, double *soa_b,
                               cudaStream_t s);
-cudaError_t launch_soa_to_aos(const Geom &g, const double *soa, int xc, int x0, double *aos, cudaStream_t s);
+cudaError_t launch_soa_to_aos(const Geom &g, const double *soa, int xc, int x0, int c, double *aos, cudaStream_t s);
 
 // mask: dense int32 [nx][ny][nz] <-> uint8 [zg][y][x]
 cudaError_t launch_mask_in(const Geom &g, const int32_t *in, uint8_t *out, int *flags, cudaStream_t s);
 cudaError_t launch_mask_out(const Geom &g, const uint8_t *in, int32_t *out, cudaStream_t s);
 
-// ghost planes when the slab is its own z neighbour (nranks == 1)
+// ghost planes when the slab is its own z neighbour (nranks == 1), fields [narrays][zg][y][x]
 cudaError_t launch_ghost_fill(const Geom &g, double *f, int narrays, cudaStream_t s);
 cudaError_t launch_ghost_fill_mask(const Geom &g, uint8_t *m, cudaStream_t s);
 
@@ -28,9 +29,9 @@ cudaError_t launch_ghost_fill_mask(const Geom &g, uint8_t *m, cudaStream_t s);
 cudaError_t launch_output(const Geom &g, int kind, const double *f, const uint8_t *mask, int c1, int c2, double *out,
                           cudaStream_t s);
 // own-site density of every site incl. ghosts (SoA -> SoA), for the wall term
-cudaError_t launch_site_density(const Geom &g, const double *fc, double *rho, cudaStream_t s);
+cudaError_t launch_site_density(const Geom &g, const double *f, int c, double *rho, cudaStream_t s);
 
 // mass and momentum of one component over physical fluid sites: partial[4*REDUCE_BLOCKS + k], k = 0..3
-cudaError_t launch_reduce(const Geom &g, const double *fc, const uint8_t *mask, double *partial, cudaStream_t s);
+cudaError_t launch_reduce(const Geom &g, const double *f, int c, const uint8_t *mask, double *partial, cudaStream_t s);
 
 }  // namespace dlbc

@@ -5,18 +5,27 @@
 
 namespace dlbc {
 
-// Device layout (DESIGN.md "Data layout in HBM"):
-//   populations  f[c][q][zg][y][x]   fp64, x fastest, zg in [0, nz+2): planes 0 and nz+1 are ghosts
+// Device layout (DESIGN.md "Data layout in HBM"), plane-major structure of arrays:
+//   populations  f[zg][c][q][y][x]   fp64, x fastest; zg in [0, nz+2): planes 0 and nz+1 are ghosts
 //   psi          psi[c][zg][y][x]    fp64, same ghosts
 //   mask         m[zg][y][x]         uint8 (0 = None, 1 = Solid), same ghosts
+// One z-plane of ALL C*19 population arrays is one contiguous block of C*19*nx*ny doubles, so
+//   * everything a site update touches (planes zg-1, zg, zg+1) lies within 3*C*19*nx*ny elements
+//     of the plane's base pointer: per-thread addressing is 32-bit offsets from a block-uniform
+//     64-bit base (3 integer instructions per access instead of ~10 with per-array 64-bit strides);
+//   * a boundary plane of one (c, q) array is still one contiguous run of nx*ny doubles for the
+//     NCCL ghost exchange, and a whole ghost plane is one contiguous copy.
 // x and y are periodic inside the kernels (the slab owns all of x and y); z neighbours come from
 // the ghost planes, which are filled by the step kernels themselves when the rank is its own
 // neighbour (nranks == 1) and by NCCL send/recv otherwise.
 struct Geom {
   int nx, ny, nz;        // local physical extents (nz = this slab's planes)
   int periodic_z_local;  // nranks == 1: the slab is its own z neighbour
-  int64_t plane;         // nx * ny
-  int64_t sites_g;       // (nz + 2) * plane  == stride between consecutive (c, q) arrays
+  int plane;             // nx * ny                      == stride between consecutive q arrays
+  int fc;                // 19 * plane                   == stride between components within a plane block
+  int fz;                // ncomp * 19 * plane           == stride between z planes of the populations
+  int ncomp;
+  int64_t sites_g;       // (nz + 2) * plane             == stride between the components of psi
 };
 
 struct Fields {
@@ -27,43 +36,65 @@ struct Fields {
   const uint8_t *mask;   // [sites_g]
 };
 
+__host__ __device__ __forceinline__ int64_t f_index(const Geom &g, int c, int q, int zg, int64_t sxy) {
+  return (int64_t)zg * g.fz + (int64_t)c * g.fc + (int64_t)q * g.plane + sxy;
+}
+
 __device__ __forceinline__ int wrap_inc(int i, int n) { return i + 1 == n ? 0 : i + 1; }
 __device__ __forceinline__ int wrap_dec(int i, int n) { return i == 0 ? n - 1 : i - 1; }
 
-// Offsets of the 3x3 rows (dy, dz in {-1,0,1}) around site (x, y, zg) and the wrapped x columns.
+// In-plane neighbourhood of site (x, y): 32-bit element offsets with the periodic wrap folded in.
 struct Nbr {
-  int64_t row[3][3];  // [dz+1][dy+1] -> index of (x=0, y+dy, zg+dz)
-  int xc[3];          // [dx+1] -> wrapped x
-  __device__ __forceinline__ int64_t at(int dx, int dy, int dz) const { return row[dz + 1][dy + 1] + xc[dx + 1]; }
+  int sxy;    // y * nx + x
+  int ox[3];  // [dx+1]: offset to x+dx  (-1 / +1, or +-(nx-1) across the periodic boundary)
+  int oy[3];  // [dy+1]: offset to y+dy  (-nx / +nx, or +-(ny-1)*nx)
+  __device__ __forceinline__ int at(int dx, int dy) const { return sxy + ox[dx + 1] + oy[dy + 1]; }
 };
 
-__device__ __forceinline__ Nbr make_nbr(const Geom &g, int x, int y, int zg) {
+__device__ __forceinline__ Nbr make_nbr(const Geom &g, int x, int y) {
   Nbr n;
-  const int ys[3] = {wrap_dec(y, g.ny), y, wrap_inc(y, g.ny)};
-#pragma unroll
-  for (int dz = 0; dz < 3; dz++)
-#pragma unroll
-    for (int dy = 0; dy < 3; dy++) n.row[dz][dy] = ((int64_t)(zg + dz - 1) * g.ny + ys[dy]) * g.nx;
-  n.xc[0] = wrap_dec(x, g.nx);
-  n.xc[1] = x;
-  n.xc[2] = wrap_inc(x, g.nx);
+  n.sxy = y * g.nx + x;
+  n.ox[0] = x == 0 ? g.nx - 1 : -1;
+  n.ox[1] = 0;
+  n.ox[2] = x == g.nx - 1 ? 1 - g.nx : 1;
+  n.oy[0] = y == 0 ? (g.ny - 1) * g.nx : -g.nx;
+  n.oy[1] = 0;
+  n.oy[2] = y == g.ny - 1 ? -(g.ny - 1) * g.nx : g.nx;
   return n;
+}
+
+// Block-uniform base pointers of ghost-inclusive plane zg.
+__device__ __forceinline__ const double *f_plane(const double *f, const Geom &g, int zg, int c) {
+  return f + (int64_t)zg * g.fz + (int64_t)c * g.fc;
+}
+__device__ __forceinline__ double *f_plane(double *f, const Geom &g, int zg, int c) {
+  return f + (int64_t)zg * g.fz + (int64_t)c * g.fc;
+}
+__device__ __forceinline__ const uint8_t *mask_plane(const uint8_t *m, const Geom &g, int zg) {
+  return m + (int64_t)zg * g.plane;
+}
+__device__ __forceinline__ const double *psi_plane(const double *p, const Geom &g, int zg, int c) {
+  return p + (int64_t)c * g.sites_g + (int64_t)zg * g.plane;
+}
+__device__ __forceinline__ double *psi_plane(double *p, const Geom &g, int zg, int c) {
+  return p + (int64_t)c * g.sites_g + (int64_t)zg * g.plane;
 }
 
 // lb/advection.d:61-89: pull streaming with half-way bounce-back for one component at one
 // (advectable) site: f[q] = bounce-back(mask[p - c_q]) ? old[p][bounce q] : old[p - c_q][q].
+// ps = f_plane(f_old, g, zg, c) + n.sxy  (per-thread pointer to the site's q = 0 entry: every
+// access is then ps[int offset], one IMAD.WIDE), ms = mask_plane(mask, g, zg) + n.sxy.
 template <bool MASK>
-__device__ __forceinline__ void pull19(const double *__restrict__ fc, int64_t qstride,
-                                       const uint8_t *__restrict__ mask, const Nbr &n, double (&f)[Q]) {
-  const int64_t self = n.at(0, 0, 0);
+__device__ __forceinline__ void pull19(const double *__restrict__ ps, const uint8_t *__restrict__ ms, const Geom &g,
+                                       const Nbr &n, double (&f)[Q]) {
 #pragma unroll
   for (int q = 0; q < Q; q++) {
-    int64_t src = n.at(-cx(q), -cy(q), -cz(q));
-    int qq = q;
+    const int d = n.ox[1 - cx(q)] + n.oy[1 - cy(q)];  // in-plane offset to the upstream site p - c_q
+    int src = q * g.plane - cz(q) * g.fz + d;
     if (MASK && q > 0) {
-      if (mask[src]) { src = self; qq = bounce(q); }
+      if (ms[d - cz(q) * g.plane]) src = bounce(q) * g.plane;
     }
-    f[q] = __ldg(fc + (int64_t)qq * qstride + src);
+    f[q] = __ldg(ps + src);
   }
 }
 

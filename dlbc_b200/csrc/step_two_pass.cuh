@@ -10,6 +10,8 @@
 // resetForce / distributeForce vanish: the force lives in registers and forceDistributed == 0
 // when electrokinetics is off (force.d:179-197 then adds +0.0).
 //
+// Addressing: block-uniform 64-bit plane bases + 32-bit per-thread offsets (lattice.cuh).
+//
 // DRAM traffic per lattice-site update, C components: K1 reads 152 C, writes 8 C;
 // K2 reads 152 C + 8 C (+1 mask byte), writes 152 C  ==> 472 C + 1 bytes (945 B at C = 2).
 #pragma once
@@ -24,19 +26,19 @@ __global__ void __launch_bounds__(128) psi_kernel(Geom g, Fields fl, int z_begin
   if (x >= g.nx) return;
   const int y = blockIdx.y;
   const int zg = z_begin + blockIdx.z;  // ghost-inclusive plane index, 1..nz
-  const Nbr n = make_nbr(g, x, y, zg);
-  const int64_t s = n.at(0, 0, 0);
-  if (MASK && fl.mask[s]) return;  // psi of solid sites is never read (force.d:273 uses the own-site psi)
+  const Nbr n = make_nbr(g, x, y);
+  const uint8_t *ms = mask_plane(fl.mask, g, zg) + n.sxy;
+  if (MASK && ms[0]) return;  // psi of solid sites is never read (force.d:273 uses the own-site psi)
+  const double *ps = f_plane(fl.f_old, g, zg, 0) + n.sxy;
 #pragma unroll
   for (int c = 0; c < C; c++) {
     double f[Q];
-    pull19<MASK>(fl.f_old + (int64_t)c * Q * g.sites_g, g.sites_g, fl.mask, n, f);
+    pull19<MASK>(ps + c * g.fc, ms, g, n, f);
     const double v = psi_of<PSI>(density19(f));
-    double *p = fl.psi + (int64_t)c * g.sites_g;
-    p[s] = v;
+    psi_plane(fl.psi, g, zg, c)[n.sxy] = v;
     if (g.periodic_z_local) {
-      if (zg == g.nz) p[s - (int64_t)g.nz * g.plane] = v;  // -> ghost plane 0
-      if (zg == 1) p[s + (int64_t)g.nz * g.plane] = v;     // -> ghost plane nz+1
+      if (zg == g.nz) psi_plane(fl.psi, g, 0, c)[n.sxy] = v;         // -> ghost plane 0
+      if (zg == 1) psi_plane(fl.psi, g, g.nz + 1, c)[n.sxy] = v;     // -> ghost plane nz+1
     }
   }
 }
@@ -44,33 +46,17 @@ __global__ void __launch_bounds__(128) psi_kernel(Geom g, Fields fl, int z_begin
 // ---- Shan-Chen force for all components of one site (force.d:238-309) -----------------------
 // Accumulation order per component f1 is the reference's: f2 outer, q = 1..18 inner, then the
 // wall term q = 0..18; prefactor = ((w_q * psi1) * psi2) * cc.
-template <int C, bool MASK>
-__device__ __forceinline__ void shan_chen_force(const Geom &g, const Fields &fl, const StepParams &P,
+template <int C, bool MASK, bool EXACT>
+__device__ __forceinline__ void shan_chen_force(const Geom &g, const Fields &fl, const StepParams &P, int zg,
                                                 const Nbr &n, const double (&psi1)[C], double (&F)[C][3]) {
-  const int64_t s = n.at(0, 0, 0);
-#pragma unroll
-  for (int f2 = 0; f2 < C; f2++) {
-    bool any = false;
-#pragma unroll
-    for (int f1 = 0; f1 < C; f1++) any |= (P.gcc[f1 * MAXC + f2] != 0.0);
-    if (!any) continue;
-    const double *__restrict__ psi2p = fl.psi + (int64_t)f2 * g.sites_g;
-#pragma unroll
-    for (int q = 1; q < Q; q++) {
-      int64_t nb = n.at(cx(q), cy(q), cz(q));
-      if (MASK) { if (fl.mask[nb]) nb = s; }
-      const double psi2 = (MASK && nb == s) ? psi1[f2] : __ldg(psi2p + nb);
-#pragma unroll
-      for (int f1 = 0; f1 < C; f1++) {
-        const double cc = P.gcc[f1 * MAXC + f2];
-        if (cc == 0.0) continue;
-        const double pref = weight(q) * psi1[f1] * psi2 * cc;
-        if (cx(q) == 1) F[f1][0] -= pref; else if (cx(q) == -1) F[f1][0] += pref;
-        if (cy(q) == 1) F[f1][1] -= pref; else if (cy(q) == -1) F[f1][1] += pref;
-        if (cz(q) == 1) F[f1][2] -= pref; else if (cz(q) == -1) F[f1][2] += pref;
-      }
-    }
-  }
+  const uint8_t *ms = mask_plane(fl.mask, g, zg) + n.sxy;
+  const double *__restrict__ pp = psi_plane(fl.psi, g, zg, 0) + n.sxy;
+  const int64_t cstride = g.sites_g;
+  sc_force<C, EXACT>(P, psi1, F, [&](int f2, int q) -> double {
+    const int d = n.ox[1 + cx(q)] + n.oy[1 + cy(q)] + cz(q) * g.plane;
+    if (MASK && ms[d]) return psi1[f2];
+    return __ldg(pp + f2 * cstride + d);
+  });
 }
 
 // NOTE on ordering: the reference finishes ALL f2 for a given f1 (then the wall term of f1)
@@ -78,17 +64,18 @@ __device__ __forceinline__ void shan_chen_force(const Geom &g, const Fields &fl,
 // f1 loops as above leaves each F[f1]'s operation sequence unchanged.
 
 template <int C>
-__device__ __forceinline__ void wall_force(const Geom &g, const Fields &fl, const StepParams &P,
+__device__ __forceinline__ void wall_force(const Geom &g, const Fields &fl, const StepParams &P, int zg,
                                            const Nbr &n, const double (&psi1)[C], double (&F)[C][3]) {
+  const uint8_t *mp = mask_plane(fl.mask, g, zg);
 #pragma unroll
   for (int f1 = 0; f1 < C; f1++) {
     const double wc = P.gwc[f1];
     if (wc == 0.0) continue;
-    const double *__restrict__ rw = fl.rho_wall + (int64_t)f1 * g.sites_g;
+    const double *__restrict__ rw = psi_plane(fl.rho_wall, g, zg, f1);  // same [c][zg][y][x] layout as psi
 #pragma unroll
     for (int q = 0; q < Q; q++) {
-      const int64_t nb = n.at(cx(q), cy(q), cz(q));
-      if (fl.mask[nb]) {
+      const int nb = n.at(cx(q), cy(q)) + cz(q) * g.plane;
+      if (mp[nb]) {
         const double pref = weight(q) * psi1[f1] * rw[nb] * wc;
         if (cx(q) == 1) F[f1][0] -= pref; else if (cx(q) == -1) F[f1][0] += pref;
         if (cy(q) == 1) F[f1][1] -= pref; else if (cy(q) == -1) F[f1][1] += pref;
@@ -119,22 +106,45 @@ __device__ __forceinline__ void common_velocity(const StepParams &P, const doubl
 }
 
 // ---- K2 -------------------------------------------------------------------------------------
+// Store one component's post-collision populations of site (plane zg, sxy) and, when the slab is
+// its own z neighbour, fill next step's ghost planes with the populations that will cross the
+// periodic boundary (only c_z = +1 upward, c_z = -1 downward).
+__device__ __forceinline__ void store19(const Geom &g, double *__restrict__ f_new, int zg, int c, int sxy,
+                                        const double (&f)[Q]) {
+  double *__restrict__ out = f_plane(f_new, g, zg, c) + sxy;
+#pragma unroll
+  for (int q = 0; q < Q; q++) out[q * g.plane] = f[q];
+  if (g.periodic_z_local) {
+    if (zg == g.nz) {
+      double *__restrict__ gh = f_plane(f_new, g, 0, c) + sxy;
+#pragma unroll
+      for (int q = 0; q < Q; q++) if (cz(q) == 1) gh[q * g.plane] = f[q];
+    }
+    if (zg == 1) {
+      double *__restrict__ gh = f_plane(f_new, g, g.nz + 1, c) + sxy;
+#pragma unroll
+      for (int q = 0; q < Q; q++) if (cz(q) == -1) gh[q * g.plane] = f[q];
+    }
+  }
+}
+
 template <int C, int EQ, bool SC, bool MASK, bool EXACT>
 __global__ void __launch_bounds__(128, (MASK && SC) ? 3 : 4) fused_kernel(Geom g, Fields fl, StepParams P, int z_begin) {
   const int x = blockIdx.x * blockDim.x + threadIdx.x;
   if (x >= g.nx) return;
   const int y = blockIdx.y;
   const int zg = z_begin + blockIdx.z;
-  const Nbr n = make_nbr(g, x, y, zg);
-  const int64_t s = n.at(0, 0, 0);
+  const Nbr n = make_nbr(g, x, y);
+  const uint8_t *ms = mask_plane(fl.mask, g, zg) + n.sxy;
   // Solid sites: advection copies them (advection.d:83-85) and they never collide; both
   // population buffers hold their (static) values since upload, so there is nothing to do.
-  if (MASK && fl.mask[s]) return;
+  if (MASK && ms[0]) return;
 
   double f[C][Q], rho[C], m[C][3], F[C][3];
+  const double *ps = f_plane(fl.f_old, g, zg, 0) + n.sxy;
 #pragma unroll
   for (int c = 0; c < C; c++) {
-    pull19<MASK>(fl.f_old + (int64_t)c * Q * g.sites_g, g.sites_g, fl.mask, n, f[c]);
+    pull19<MASK>(ps + c * g.fc, ms, g, n, f[c]);
     rho[c] = density19(f[c]);
     momentum19(f[c], m[c]);
     F[c][0] = 0.0; F[c][1] = 0.0; F[c][2] = 0.0;
@@ -142,33 +152,23 @@ __global__ void __launch_bounds__(128, (MASK && SC) ? 3 : 4) fused_kernel(Geom g
   if (SC) {
     double psi1[C];
 #pragma unroll
-    for (int c = 0; c < C; c++) psi1[c] = fl.psi[(int64_t)c * g.sites_g + s];
-    shan_chen_force<C, MASK>(g, fl, P, n, psi1, F);
-    if (MASK && P.any_gwc) wall_force<C>(g, fl, P, n, psi1, F);
+    for (int c = 0; c < C; c++) psi1[c] = psi_plane(fl.psi, g, zg, c)[n.sxy];
+    shan_chen_force<C, MASK, EXACT>(g, fl, P, zg, n, psi1, F);
+    if (MASK && P.any_gwc) wall_force<C>(g, fl, P, zg, n, psi1, F);
   }
   double u[3] = {0.0, 0.0, 0.0};
   if (EQ == 2) common_velocity<C, EXACT>(P, m, rho, u);
 #pragma unroll
   for (int c = 0; c < C; c++) {
     collide_site<EQ, EXACT>(f[c], rho[c], m[c], F[c], u, P, c);
-    double *__restrict__ out = fl.f_new + (int64_t)c * Q * g.sites_g;
-#pragma unroll
-    for (int q = 0; q < Q; q++) {
-      out[(int64_t)q * g.sites_g + s] = f[c][q];
-      // the slab is its own z neighbour: fill next step's ghost planes with the populations that
-      // will cross the periodic boundary (only c_z = +1 upward, c_z = -1 downward)
-      if (g.periodic_z_local) {
-        if (cz(q) == 1 && zg == g.nz) out[(int64_t)q * g.sites_g + s - (int64_t)g.nz * g.plane] = f[c][q];
-        if (cz(q) == -1 && zg == 1) out[(int64_t)q * g.sites_g + s + (int64_t)g.nz * g.plane] = f[c][q];
-      }
-    }
+    store19(g, fl.f_new, zg, c, n.sxy, f[c]);
   }
 }
 
 // ---- L.force[comp] for output (lb/io.d:86-90) -----------------------------------------------
 // Not on the per-step path: the step kernels keep the force in registers.  Recomputed from the
 // psi field of the last step; zero on solid sites (resetForce, force.d:165-170, and the
-// isCollidable test at force.d:258).
+// isCollidable test at force.d:258).  out: SoA vector field [3][sites_g].
 template <int C, bool MASK>
 __global__ void __launch_bounds__(128) force_kernel(Geom g, Fields fl, StepParams P, int comp,
                                                     double *__restrict__ out, int z_begin) {
@@ -176,18 +176,18 @@ __global__ void __launch_bounds__(128) force_kernel(Geom g, Fields fl, StepParam
   if (x >= g.nx) return;
   const int y = blockIdx.y;
   const int zg = z_begin + blockIdx.z;
-  const Nbr n = make_nbr(g, x, y, zg);
-  const int64_t s = n.at(0, 0, 0);
+  const Nbr n = make_nbr(g, x, y);
   double F[C][3];
 #pragma unroll
   for (int c = 0; c < C; c++) { F[c][0] = 0.0; F[c][1] = 0.0; F[c][2] = 0.0; }
-  if (!(MASK && fl.mask[s])) {
+  if (!(MASK && mask_plane(fl.mask, g, zg)[n.sxy])) {
     double psi1[C];
 #pragma unroll
-    for (int c = 0; c < C; c++) psi1[c] = fl.psi[(int64_t)c * g.sites_g + s];
-    shan_chen_force<C, MASK>(g, fl, P, n, psi1, F);
-    if (MASK && P.any_gwc) wall_force<C>(g, fl, P, n, psi1, F);
+    for (int c = 0; c < C; c++) psi1[c] = psi_plane(fl.psi, g, zg, c)[n.sxy];
+    shan_chen_force<C, MASK, true>(g, fl, P, zg, n, psi1, F);
+    if (MASK && P.any_gwc) wall_force<C>(g, fl, P, zg, n, psi1, F);
   }
+  const int64_t s = (int64_t)zg * g.plane + n.sxy;
 #pragma unroll
   for (int c = 0; c < C; c++) {
     if (c == comp) {

@@ -50,14 +50,15 @@ __device__ __forceinline__ int wrap_coord(int i, int n) {
 template <int C, int PSI, bool MASK>
 __device__ __forceinline__ bool pull_site(const Geom &g, const Fields &fl, int x, int y, int w, double (&f)[C][Q],
                                           double (&psi)[C]) {
-  const Nbr n = make_nbr(g, x, y, w);
-  if (MASK && fl.mask[n.at(0, 0, 0)]) {
+  const Nbr n = make_nbr(g, x, y);
+  const uint8_t *ms = mask_plane(fl.mask, g, w) + n.sxy;
+  if (MASK && ms[0]) {
 #pragma unroll
     for (int c = 0; c < C; c++) psi[c] = 0.0;  // never read: bounced links use the reader's own psi (force.d:273)
     return false;
   }
 #pragma unroll
-  for (int c = 0; c < C; c++) pull19<MASK>(fl.f_old + (int64_t)c * Q * g.sites_g, g.sites_g, fl.mask, n, f[c]);
+  for (int c = 0; c < C; c++) pull19<MASK>(f_plane(fl.f_old, g, w, c) + n.sxy, ms, g, n, f[c]);
 #pragma unroll
   for (int c = 0; c < C; c++) psi[c] = psi_of<PSI>(density19(f[c]));
   return true;
@@ -149,8 +150,9 @@ __global__ void __launch_bounds__(TX *TY, MINB) zmarch_kernel(Geom g, Fields fl,
 
     // ---- C: force + collide plane zg, write once
     if (!inside) continue;
-    const int64_t s = ((int64_t)zg * g.ny + y) * g.nx + x;
-    if (MASK && fl.mask[s]) continue;  // solid sites keep their populations in both buffers
+    const Nbr n = make_nbr(g, xs, ys);
+    const uint8_t *mp = mask_plane(fl.mask, g, zg);
+    if (MASK && mp[n.sxy]) continue;  // solid sites keep their populations in both buffers
     double rho[C], m[C][3], F[C][3], psi1[C];
     const double *r0 = ring + (zg & 3) * C * RP;
 #pragma unroll
@@ -160,46 +162,18 @@ __global__ void __launch_bounds__(TX *TY, MINB) zmarch_kernel(Geom g, Fields fl,
       F[c][0] = 0.0; F[c][1] = 0.0; F[c][2] = 0.0;
       psi1[c] = r0[c * RP + cell];
     }
-    // addShanChenForcePsi (force.d:238-309); same accumulation order as shan_chen_force()
-    Nbr n;
-    if (MASK) n = make_nbr(g, x, y, zg);
-#pragma unroll
-    for (int f2 = 0; f2 < C; f2++) {
-      bool any = false;
-#pragma unroll
-      for (int f1 = 0; f1 < C; f1++) any |= (P.gcc[f1 * MAXC + f2] != 0.0);
-      if (!any) continue;
-#pragma unroll
-      for (int q = 1; q < Q; q++) {
-        const double *rq = ring + ((zg + cz(q)) & 3) * C * RP + f2 * RP;
-        double psi2 = rq[cell + cy(q) * RW + cx(q)];
-        if (MASK) { if (fl.mask[n.at(cx(q), cy(q), cz(q))]) psi2 = psi1[f2]; }
-#pragma unroll
-        for (int f1 = 0; f1 < C; f1++) {
-          const double cc = P.gcc[f1 * MAXC + f2];
-          if (cc == 0.0) continue;
-          const double pref = weight(q) * psi1[f1] * psi2 * cc;
-          if (cx(q) == 1) F[f1][0] -= pref; else if (cx(q) == -1) F[f1][0] += pref;
-          if (cy(q) == 1) F[f1][1] -= pref; else if (cy(q) == -1) F[f1][1] += pref;
-          if (cz(q) == 1) F[f1][2] -= pref; else if (cz(q) == -1) F[f1][2] += pref;
-        }
-      }
-    }
-    if (MASK && P.any_gwc) wall_force<C>(g, fl, P, n, psi1, F);
+    // addShanChenForcePsi (force.d:238-309): neighbours' psi from the shared-memory ring
+    sc_force<C, EXACT>(P, psi1, F, [&](int f2, int q) -> double {
+      if (MASK) { if (mp[n.at(cx(q), cy(q)) + cz(q) * g.plane]) return psi1[f2]; }
+      return ring[(((zg + cz(q)) & 3) * C + f2) * RP + cell + cy(q) * RW + cx(q)];
+    });
+    if (MASK && P.any_gwc) wall_force<C>(g, fl, P, zg, n, psi1, F);
     double u[3] = {0.0, 0.0, 0.0};
     if (EQ == 2) common_velocity<C, EXACT>(P, m, rho, u);
 #pragma unroll
     for (int c = 0; c < C; c++) {
       collide_site<EQ, EXACT>(f[c], rho[c], m[c], F[c], u, P, c);
-      double *__restrict__ out = fl.f_new + (int64_t)c * Q * g.sites_g;
-#pragma unroll
-      for (int q = 0; q < Q; q++) {
-        out[(int64_t)q * g.sites_g + s] = f[c][q];
-        if (g.periodic_z_local) {
-          if (cz(q) == 1 && zg == g.nz) out[(int64_t)q * g.sites_g + s - (int64_t)g.nz * g.plane] = f[c][q];
-          if (cz(q) == -1 && zg == 1) out[(int64_t)q * g.sites_g + s + (int64_t)g.nz * g.plane] = f[c][q];
-        }
-      }
+      store19(g, fl.f_new, zg, c, n.sxy, f[c]);
     }
   }
 }
