@@ -27,11 +27,13 @@ struct KernelSet {
   force_fn force;
   launch_fn fused[2];   // [exact]
   launch_fn zmarch[2];  // [exact]
+  launch_fn zpipe[2];   // [exact]
 };
 
 #define DLBC_SET(NC)                                                                                      \
   { launch_psi_c##NC, launch_force_c##NC, {launch_fused_fast_c##NC, launch_fused_exact_c##NC},            \
-    {launch_zmarch_fast_c##NC, launch_zmarch_exact_c##NC} }
+    {launch_zmarch_fast_c##NC, launch_zmarch_exact_c##NC},                                                \
+    {launch_zpipe_fast_c##NC, launch_zpipe_exact_c##NC} }
 const KernelSet kKernels[DLBC_CUDA_MAX_COMPONENTS] = {DLBC_SET(1), DLBC_SET(2), DLBC_SET(3), DLBC_SET(4)};
 #undef DLBC_SET
 
@@ -260,21 +262,42 @@ int step_once(dlbc_cuda_ctx *ctx, KernelTimer *kt) {
   const int exact = ctx->cfg.arithmetic == DLBC_ARITH_EXACT ? 1 : 0;
   const int nz = ctx->g.nz;
   const bool sc = ctx->cfg.enable_shan_chen != 0;
-  const bool zmarch = ctx->variant == DLBC_KERNEL_ZMARCH;
+  const bool single_pass = ctx->variant == DLBC_KERNEL_ZMARCH || ctx->variant == DLBC_KERNEL_ZPIPE;
   StepLaunch L = make_launch(ctx, ctx->compute);
-  launch_fn fused = zmarch ? K.zmarch[exact] : K.fused[exact];
+  launch_fn fused = ctx->variant == DLBC_KERNEL_ZPIPE ? K.zpipe[exact]
+                    : ctx->variant == DLBC_KERNEL_ZMARCH ? K.zmarch[exact] : K.fused[exact];
+  const char *fused_name = ctx->variant == DLBC_KERNEL_ZPIPE ? "zpipe_kernel"
+                           : ctx->variant == DLBC_KERNEL_ZMARCH ? "zmarch_kernel" : "fused_kernel";
 
   if (ctx->cfg.nranks == 1) {
-    if (sc && !zmarch) {
+    if (sc && !single_pass) {
       if (kt) kt->begin("psi_kernel");
       CK(K.psi(L, 1, nz));
       ctx->launches++;
       if (kt) kt->end();
     }
-    if (kt) kt->begin(zmarch ? "zmarch_kernel" : "fused_kernel");
+    if (kt) kt->begin(fused_name);
     CK(fused(L, 1, nz));
     ctx->launches++;
     if (kt) kt->end();
+  } else if (single_pass) {
+    // z-slab ring, single-pass kernel.  The interior planes 2..nz-1 need nothing from this step's
+    // exchanges (psi of planes 1 and nz is computed inside the kernel from populations whose ghost
+    // planes arrived at the end of the previous step), so they run on the compute stream while
+    // the high-priority comm stream runs the boundary chain: psi of planes 1 and nz -> NCCL psi
+    // ghost exchange -> planes 1 and nz -> NCCL exchange of the 5 crossing populations per side.
+    StepLaunch Lb = make_launch(ctx, ctx->comm);
+    CK(cudaStreamWaitEvent(ctx->compute, ctx->ev_ghost_f, 0));
+    CK(cudaEventRecord(ctx->ev_bnd, ctx->compute));
+    CK(cudaStreamWaitEvent(ctx->comm, ctx->ev_bnd, 0));
+    CK(K.psi(Lb, 1, 1)); ctx->launches++;
+    if (nz > 1) { CK(K.psi(Lb, nz, 1)); ctx->launches++; }
+    TRY(exchange_planes<double>(ctx, scalar_xfer(ctx, ctx->psi, ctx->cfg.ncomp), ncclDouble, ctx->comm));
+    CK(fused(Lb, 1, 1)); ctx->launches++;
+    if (nz > 1) { CK(fused(Lb, nz, 1)); ctx->launches++; }
+    TRY(exchange_planes<double>(ctx, population_xfer(ctx, ctx->f[1 - ctx->cur]), ncclDouble, ctx->comm));
+    CK(cudaEventRecord(ctx->ev_ghost_f, ctx->comm));
+    if (nz > 2) { CK(fused(L, 2, nz - 2)); ctx->launches++; }
   } else {
     // z-slab ring.  compute stream: K1 boundary planes | K1 interior | K2 boundary | K2 interior;
     // comm stream: psi ghost exchange (overlaps K1 interior), f ghost exchange (overlaps K2
@@ -437,7 +460,7 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
   ARG(cfg->psi_form == DLBC_PSI_LINEAR || cfg->psi_form == DLBC_PSI_EXPONENTIAL, "create: bad psi_form");
   ARG(cfg->eqdist_form >= 0 && cfg->eqdist_form <= 2, "create: bad eqdist_form");
   ARG(cfg->arithmetic == DLBC_ARITH_FAST || cfg->arithmetic == DLBC_ARITH_EXACT, "create: bad arithmetic mode");
-  ARG(cfg->kernel_variant >= DLBC_KERNEL_AUTO && cfg->kernel_variant <= DLBC_KERNEL_ZMARCH, "create: bad kernel_variant");
+  ARG(cfg->kernel_variant >= DLBC_KERNEL_AUTO && cfg->kernel_variant <= DLBC_KERNEL_ZPIPE, "create: bad kernel_variant");
   for (int c = 0; c < cfg->ncomp; c++) ARG(cfg->tau[c] > 0.0 && std::isfinite(cfg->tau[c]), "create: tau must be positive");
 
   int ndev = 0;
@@ -495,11 +518,17 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
   for (int d = 0; d < 3; d++) p.gacc[d] = cfg->global_acc[d];
 
   ctx->variant = cfg->kernel_variant == DLBC_KERNEL_AUTO ? DLBC_KERNEL_TWO_PASS : cfg->kernel_variant;
-  if (!cfg->enable_shan_chen || cfg->nranks > 1) ctx->variant = DLBC_KERNEL_TWO_PASS;
+  if (!cfg->enable_shan_chen) ctx->variant = DLBC_KERNEL_TWO_PASS;
+  if (cfg->nranks > 1 && ctx->variant == DLBC_KERNEL_ZMARCH) ctx->variant = DLBC_KERNEL_TWO_PASS;  // no ghost-psi path
   if (cfg->ncomp > 2) ctx->variant = DLBC_KERNEL_TWO_PASS;  // 19 C doubles per thread must stay in registers
 
   CKC(cudaStreamCreateWithFlags(&ctx->compute, cudaStreamNonBlocking));
-  CKC(cudaStreamCreateWithFlags(&ctx->comm, cudaStreamNonBlocking));
+  {
+    // the boundary chain of a multi-rank step must overtake the interior kernel's queued blocks
+    int prio_lo = 0, prio_hi = 0;
+    CKC(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    CKC(cudaStreamCreateWithPriority(&ctx->comm, cudaStreamNonBlocking, prio_hi));
+  }
   CKC(cudaEventCreate(&ctx->ev_a));
   CKC(cudaEventCreate(&ctx->ev_b));
   CKC(cudaEventCreateWithFlags(&ctx->ev_bnd, cudaEventDisableTiming));

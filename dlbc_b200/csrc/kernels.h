@@ -28,7 +28,9 @@ typedef cudaError_t (*force_fn)(const StepLaunch &, int comp, double *out, int z
   cudaError_t launch_fused_exact_c##NC(const StepLaunch &, int, int);                \
   cudaError_t launch_fused_fast_c##NC(const StepLaunch &, int, int);                 \
   cudaError_t launch_zmarch_exact_c##NC(const StepLaunch &, int, int);               \
-  cudaError_t launch_zmarch_fast_c##NC(const StepLaunch &, int, int);
+  cudaError_t launch_zmarch_fast_c##NC(const StepLaunch &, int, int);               \
+  cudaError_t launch_zpipe_exact_c##NC(const StepLaunch &, int, int);                \
+  cudaError_t launch_zpipe_fast_c##NC(const StepLaunch &, int, int);
 DLBC_DECLARE_STEP(1)
 DLBC_DECLARE_STEP(2)
 DLBC_DECLARE_STEP(3)

@@ -5,6 +5,7 @@
 #include "kernels.h"
 #include "step_two_pass.cuh"
 #include "step_zmarch.cuh"
+#include "step_zpipe.cuh"
 #include <cstdlib>
 
 namespace dlbc {
@@ -109,6 +110,59 @@ cudaError_t DLBC_MODE_NAME(launch_zmarch)(const StepLaunch &L, int z_begin, int 
     case 0: return zmarch_eq<DLBC_NC, 0>(L, z_begin, z_count);
     case 1: return zmarch_eq<DLBC_NC, 1>(L, z_begin, z_count);
     case 2: return zmarch_eq<DLBC_NC, 2>(L, z_begin, z_count);
+    default: return cudaErrorInvalidValue;
+  }
+#else
+  (void)z_begin;
+  return cudaErrorNotSupported;
+#endif
+}
+
+// ---- asynchronously pipelined z-march (step_zpipe.cuh) ----
+#if DLBC_NC <= 2
+template <int C, int EQ, int PSI, bool MASK, int TX, int TY>
+static cudaError_t zpipe_launch(const StepLaunch &L, int z_begin, int z_count, int chunk) {
+  auto kern = zpipe_kernel<C, EQ, PSI, MASK, kExact, TX, TY>;
+  constexpr int NT = TX * TY, NRIM = 2 * (TX + 2) + 2 * TY, RP = (TX + 2) * (TY + 2);
+  constexpr size_t smem = (size_t)(2 * C * Q * NT + C * Q * NRIM + 4 * C * RP) * sizeof(double);
+  static_assert(smem <= 227 * 1024, "zpipe tile does not fit in shared memory");
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  ZMarch zm{z_begin, z_begin + z_count, chunk};
+  dim3 grid((L.g.nx + TX - 1) / TX, (L.g.ny + TY - 1) / TY, (z_count + chunk - 1) / chunk);
+  kern<<<grid, dim3(TX, TY), smem, L.stream>>>(L.g, L.f, L.p, zm);
+  return cudaGetLastError();
+}
+
+template <int C, int EQ, int PSI, bool MASK>
+static cudaError_t zpipe_tile(const StepLaunch &L, int z_begin, int z_count) {
+  static const char *tile = std::getenv("DLBC_ZP_TILE");
+  static const char *ch = std::getenv("DLBC_ZP_CHUNK");
+  int chunk = ch ? std::atoi(ch) : 128;
+  if (chunk < 1) chunk = 128;
+  if (tile && tile[0] == '6') return zpipe_launch<C, EQ, PSI, MASK, 64, 4>(L, z_begin, z_count, chunk);
+  return zpipe_launch<C, EQ, PSI, MASK, 32, 8>(L, z_begin, z_count, chunk);
+}
+
+template <int C, int EQ>
+static cudaError_t zpipe_eq(const StepLaunch &L, int z_begin, int z_count) {
+  if (L.psi == 0) return L.mask ? zpipe_tile<C, EQ, 0, true>(L, z_begin, z_count) : zpipe_tile<C, EQ, 0, false>(L, z_begin, z_count);
+  return L.mask ? zpipe_tile<C, EQ, 1, true>(L, z_begin, z_count) : zpipe_tile<C, EQ, 1, false>(L, z_begin, z_count);
+}
+#endif
+
+cudaError_t DLBC_MODE_NAME(launch_zpipe)(const StepLaunch &L, int z_begin, int z_count) {
+  if (z_count <= 0) return cudaSuccess;
+#if DLBC_NC <= 2
+  if (!L.sc) return cudaErrorNotSupported;
+  switch (L.eq) {
+    case 0: return zpipe_eq<DLBC_NC, 0>(L, z_begin, z_count);
+    case 1: return zpipe_eq<DLBC_NC, 1>(L, z_begin, z_count);
+    case 2: return zpipe_eq<DLBC_NC, 2>(L, z_begin, z_count);
     default: return cudaErrorInvalidValue;
   }
 #else

@@ -55,7 +55,9 @@ enum {
 enum {
   DLBC_KERNEL_AUTO = 0,
   DLBC_KERNEL_TWO_PASS = 1,   /* psi kernel + fused pull/force/collide kernel (psi via L1/L2) */
-  DLBC_KERNEL_ZMARCH = 2      /* single pass: z-marching fused kernel, psi planes in shared memory */
+  DLBC_KERNEL_ZMARCH = 2,     /* single pass: z-marching fused kernel, psi planes in shared memory */
+  DLBC_KERNEL_ZPIPE = 3       /* single pass: z-march with the population loads as an asynchronous
+                                 cp.async shared-memory pipeline (loads of plane z+2 overlap plane z) */
 };
 
 /* Replaces: the module-level parameters the timestep reads -- lattice.gn (lattice.d:28),
