@@ -334,7 +334,7 @@ def main():
     ap.add_argument("--shape", default=None, help="nx,ny,nz per GPU (overrides --size; profiling runs)")
     ap.add_argument("--components", type=int, default=2)
     ap.add_argument("--arith", default="fast", choices=["fast", "exact"])
-    ap.add_argument("--kernel", default="auto", choices=["auto", "two_pass", "zmarch", "zpipe"])
+    ap.add_argument("--kernel", default="auto", choices=["auto", "two_pass", "zmarch", "zpipe", "wave"])
     ap.add_argument("--cpu-sample", type=int, default=128)
     ap.add_argument("--cpu-steps", type=int, default=20)
     ap.add_argument("--no-cpu-baseline", action="store_true")

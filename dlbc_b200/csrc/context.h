@@ -35,6 +35,7 @@ struct dlbc_cuda_ctx {
   size_t stage_bytes = 0;
   double *partial = nullptr;          // device, reduction partials
   int *flags = nullptr;               // device, [2]: bad mask value seen, solid count
+  int *wave_sync[3] = {nullptr, nullptr, nullptr};  // wave variant: ticket + counters (interior, lower, upper boundary launch)
 
   // multi-rank
   ncclComm *nccl = nullptr;

@@ -28,12 +28,14 @@ struct KernelSet {
   launch_fn fused[2];   // [exact]
   launch_fn zmarch[2];  // [exact]
   launch_fn zpipe[2];   // [exact]
+  launch_fn wave[2];    // [exact]
 };
 
 #define DLBC_SET(NC)                                                                                      \
   { launch_psi_c##NC, launch_force_c##NC, {launch_fused_fast_c##NC, launch_fused_exact_c##NC},            \
     {launch_zmarch_fast_c##NC, launch_zmarch_exact_c##NC},                                                \
-    {launch_zpipe_fast_c##NC, launch_zpipe_exact_c##NC} }
+    {launch_zpipe_fast_c##NC, launch_zpipe_exact_c##NC},                                                  \
+    {launch_wave_fast_c##NC, launch_wave_exact_c##NC} }
 const KernelSet kKernels[DLBC_CUDA_MAX_COMPONENTS] = {DLBC_SET(1), DLBC_SET(2), DLBC_SET(3), DLBC_SET(4)};
 #undef DLBC_SET
 
@@ -116,6 +118,7 @@ StepLaunch make_launch(dlbc_cuda_ctx *ctx, cudaStream_t s) {
   L.sc = ctx->cfg.enable_shan_chen;
   L.mask = ctx->has_solid ? 1 : 0;
   L.stream = s;
+  L.wave_sync = ctx->wave_sync[0];
   return L;
 }
 
@@ -262,11 +265,14 @@ int step_once(dlbc_cuda_ctx *ctx, KernelTimer *kt) {
   const int exact = ctx->cfg.arithmetic == DLBC_ARITH_EXACT ? 1 : 0;
   const int nz = ctx->g.nz;
   const bool sc = ctx->cfg.enable_shan_chen != 0;
-  const bool single_pass = ctx->variant == DLBC_KERNEL_ZMARCH || ctx->variant == DLBC_KERNEL_ZPIPE;
+  const bool single_pass = ctx->variant == DLBC_KERNEL_ZMARCH || ctx->variant == DLBC_KERNEL_ZPIPE ||
+                           ctx->variant == DLBC_KERNEL_WAVE;
   StepLaunch L = make_launch(ctx, ctx->compute);
-  launch_fn fused = ctx->variant == DLBC_KERNEL_ZPIPE ? K.zpipe[exact]
+  launch_fn fused = ctx->variant == DLBC_KERNEL_WAVE ? K.wave[exact]
+                    : ctx->variant == DLBC_KERNEL_ZPIPE ? K.zpipe[exact]
                     : ctx->variant == DLBC_KERNEL_ZMARCH ? K.zmarch[exact] : K.fused[exact];
-  const char *fused_name = ctx->variant == DLBC_KERNEL_ZPIPE ? "zpipe_kernel"
+  const char *fused_name = ctx->variant == DLBC_KERNEL_WAVE ? "wave_kernel"
+                           : ctx->variant == DLBC_KERNEL_ZPIPE ? "zpipe_kernel"
                            : ctx->variant == DLBC_KERNEL_ZMARCH ? "zmarch_kernel" : "fused_kernel";
 
   if (ctx->cfg.nranks == 1) {
@@ -286,7 +292,9 @@ int step_once(dlbc_cuda_ctx *ctx, KernelTimer *kt) {
     // planes arrived at the end of the previous step), so they run on the compute stream while
     // the high-priority comm stream runs the boundary chain: psi of planes 1 and nz -> NCCL psi
     // ghost exchange -> planes 1 and nz -> NCCL exchange of the 5 crossing populations per side.
-    StepLaunch Lb = make_launch(ctx, ctx->comm);
+    StepLaunch Lb = make_launch(ctx, ctx->comm), Lb2 = make_launch(ctx, ctx->comm);
+    Lb.wave_sync = ctx->wave_sync[1];
+    Lb2.wave_sync = ctx->wave_sync[2];
     CK(cudaStreamWaitEvent(ctx->compute, ctx->ev_ghost_f, 0));
     CK(cudaEventRecord(ctx->ev_bnd, ctx->compute));
     CK(cudaStreamWaitEvent(ctx->comm, ctx->ev_bnd, 0));
@@ -294,7 +302,7 @@ int step_once(dlbc_cuda_ctx *ctx, KernelTimer *kt) {
     if (nz > 1) { CK(K.psi(Lb, nz, 1)); ctx->launches++; }
     TRY(exchange_planes<double>(ctx, scalar_xfer(ctx, ctx->psi, ctx->cfg.ncomp), ncclDouble, ctx->comm));
     CK(fused(Lb, 1, 1)); ctx->launches++;
-    if (nz > 1) { CK(fused(Lb, nz, 1)); ctx->launches++; }
+    if (nz > 1) { CK(fused(Lb2, nz, 1)); ctx->launches++; }
     TRY(exchange_planes<double>(ctx, population_xfer(ctx, ctx->f[1 - ctx->cur]), ncclDouble, ctx->comm));
     CK(cudaEventRecord(ctx->ev_ghost_f, ctx->comm));
     if (nz > 2) { CK(fused(L, 2, nz - 2)); ctx->launches++; }
@@ -439,6 +447,7 @@ int dlbc_cuda_destroy(dlbc_cuda_ctx *ctx) {
   if (ctx->mask) cudaFree(ctx->mask);
   if (ctx->stage) cudaFree(ctx->stage);
   if (ctx->flags) cudaFree(ctx->flags);
+  for (int *p : ctx->wave_sync) if (p) cudaFree(p);
   for (cudaEvent_t e : {ctx->ev_a, ctx->ev_b, ctx->ev_bnd, ctx->ev_ghost_psi, ctx->ev_ghost_f}) if (e) cudaEventDestroy(e);
   for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
   for (cudaStream_t s : {ctx->compute, ctx->comm}) if (s) cudaStreamDestroy(s);
@@ -460,7 +469,7 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
   ARG(cfg->psi_form == DLBC_PSI_LINEAR || cfg->psi_form == DLBC_PSI_EXPONENTIAL, "create: bad psi_form");
   ARG(cfg->eqdist_form >= 0 && cfg->eqdist_form <= 2, "create: bad eqdist_form");
   ARG(cfg->arithmetic == DLBC_ARITH_FAST || cfg->arithmetic == DLBC_ARITH_EXACT, "create: bad arithmetic mode");
-  ARG(cfg->kernel_variant >= DLBC_KERNEL_AUTO && cfg->kernel_variant <= DLBC_KERNEL_ZPIPE, "create: bad kernel_variant");
+  ARG(cfg->kernel_variant >= DLBC_KERNEL_AUTO && cfg->kernel_variant <= DLBC_KERNEL_WAVE, "create: bad kernel_variant");
   for (int c = 0; c < cfg->ncomp; c++) ARG(cfg->tau[c] > 0.0 && std::isfinite(cfg->tau[c]), "create: tau must be positive");
 
   int ndev = 0;
@@ -520,7 +529,8 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
   ctx->variant = cfg->kernel_variant == DLBC_KERNEL_AUTO ? DLBC_KERNEL_TWO_PASS : cfg->kernel_variant;
   if (!cfg->enable_shan_chen) ctx->variant = DLBC_KERNEL_TWO_PASS;
   if (cfg->nranks > 1 && ctx->variant == DLBC_KERNEL_ZMARCH) ctx->variant = DLBC_KERNEL_TWO_PASS;  // no ghost-psi path
-  if (cfg->ncomp > 2) ctx->variant = DLBC_KERNEL_TWO_PASS;  // 19 C doubles per thread must stay in registers
+  if (cfg->ncomp > 2 && ctx->variant != DLBC_KERNEL_WAVE)
+    ctx->variant = DLBC_KERNEL_TWO_PASS;  // z-march kernels: 19 C doubles per thread must stay in registers
 
   CKC(cudaStreamCreateWithFlags(&ctx->compute, cudaStreamNonBlocking));
   {
@@ -543,7 +553,11 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
   CKC(cudaMalloc(&ctx->mask, (size_t)g.sites_g));
   CKC(cudaMalloc(&ctx->partial, (size_t)(4 * REDUCE_BLOCKS + 4) * sizeof(double)));
   CKC(cudaMalloc(&ctx->flags, 2 * sizeof(int)));
-  ctx->device_bytes = (int64_t)(2 * fbytes + sbytes + g.sites_g + (4 * REDUCE_BLOCKS + 4) * sizeof(double) + 8);
+  for (int i = 0; i < (cfg->nranks > 1 ? 3 : 1); i++) {
+    CKC(cudaMalloc(&ctx->wave_sync[i], wave_sync_ints(g, 1) * sizeof(int)));
+    ctx->device_bytes += (int64_t)(wave_sync_ints(g, 1) * sizeof(int));
+  }
+  ctx->device_bytes += (int64_t)(2 * fbytes + sbytes + g.sites_g + (4 * REDUCE_BLOCKS + 4) * sizeof(double) + 8);
   CKC(cudaMemsetAsync(ctx->f[0], 0, fbytes, ctx->compute));
   CKC(cudaMemsetAsync(ctx->f[1], 0, fbytes, ctx->compute));
   CKC(cudaMemsetAsync(ctx->psi, 0, sbytes, ctx->compute));

@@ -11,7 +11,15 @@ struct StepLaunch {
   StepParams p;
   int eq, psi, sc, mask;
   cudaStream_t stream;
+  int *wave_sync;  // ticket + completion counters of the wave variant (wave_sync_ints() ints)
 };
+
+// size of StepLaunch::wave_sync: 1 ticket + one counter per (band, ghost-inclusive plane); sized for
+// the smallest band height the launcher accepts (1 row)
+inline size_t wave_sync_ints(const Geom &g, int tyb) {
+  const int nb = (g.ny + tyb - 1) / tyb;
+  return 1 + (size_t)nb * (g.nz + 2);
+}
 
 // z_begin / z_count address ghost-inclusive planes: the physical planes are 1..nz.
 // Each returns cudaGetLastError() of its launch.  One translation unit per (component count,
@@ -30,7 +38,9 @@ typedef cudaError_t (*force_fn)(const StepLaunch &, int comp, double *out, int z
   cudaError_t launch_zmarch_exact_c##NC(const StepLaunch &, int, int);               \
   cudaError_t launch_zmarch_fast_c##NC(const StepLaunch &, int, int);               \
   cudaError_t launch_zpipe_exact_c##NC(const StepLaunch &, int, int);                \
-  cudaError_t launch_zpipe_fast_c##NC(const StepLaunch &, int, int);
+  cudaError_t launch_zpipe_fast_c##NC(const StepLaunch &, int, int);                 \
+  cudaError_t launch_wave_exact_c##NC(const StepLaunch &, int, int);                 \
+  cudaError_t launch_wave_fast_c##NC(const StepLaunch &, int, int);
 DLBC_DECLARE_STEP(1)
 DLBC_DECLARE_STEP(2)
 DLBC_DECLARE_STEP(3)

@@ -84,9 +84,40 @@ __device__ __forceinline__ double *psi_plane(double *p, const Geom &g, int zg, i
 // (advectable) site: f[q] = bounce-back(mask[p - c_q]) ? old[p][bounce q] : old[p - c_q][q].
 // ps = f_plane(f_old, g, zg, c) + n.sxy  (per-thread pointer to the site's q = 0 entry: every
 // access is then ps[int offset], one IMAD.WIDE), ms = mask_plane(mask, g, zg) + n.sxy.
-template <bool MASK>
+// L2 eviction-priority hints (createpolicy + ld/st .L2::cache_hint).  Used by the wave variant
+// (step_wave.cuh), whose psi items read populations that the fused items read again shortly
+// afterwards: first touch KEEP (evict_last), second touch and the freshly written populations
+// STREAM (evict_first), so that the written lines do not push the waiting ones out of L2.
+enum { POL_DEFAULT = 0, POL_KEEP = 1, POL_STREAM = 2 };
+
+template <int POL>
+__device__ __forceinline__ uint64_t make_policy() {
+  uint64_t p = 0;
+  if (POL == POL_KEEP) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;\n" : "=l"(p));
+  if (POL == POL_STREAM) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;\n" : "=l"(p));
+  return p;
+}
+template <int POL>
+__device__ __forceinline__ double load_pop(const double *a, uint64_t pol) {
+  if (POL == POL_DEFAULT) return __ldg(a);
+  double v;
+  asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;\n" : "=d"(v) : "l"(a), "l"(pol));
+  return v;
+}
+template <int POL>
+__device__ __forceinline__ void store_pop(double *a, double v, uint64_t pol) {
+  if (POL == POL_DEFAULT) { *a = v; return; }
+  asm volatile("st.global.L2::cache_hint.f64 [%0], %1, %2;\n" ::"l"(a), "d"(v), "l"(pol) : "memory");
+}
+
+// lb/advection.d:61-89: pull streaming with half-way bounce-back for one component at one
+// (advectable) site: f[q] = bounce-back(mask[p - c_q]) ? old[p][bounce q] : old[p - c_q][q].
+// ps = f_plane(f_old, g, zg, c) + n.sxy  (per-thread pointer to the site's q = 0 entry: every
+// access is then ps[int offset], one IMAD.WIDE), ms = mask_plane(mask, g, zg) + n.sxy.
+template <bool MASK, int POL = POL_DEFAULT>
 __device__ __forceinline__ void pull19(const double *__restrict__ ps, const uint8_t *__restrict__ ms, const Geom &g,
                                        const Nbr &n, double (&f)[Q]) {
+  const uint64_t pol = make_policy<POL>();
 #pragma unroll
   for (int q = 0; q < Q; q++) {
     const int d = n.ox[1 - cx(q)] + n.oy[1 - cy(q)];  // in-plane offset to the upstream site p - c_q
@@ -94,7 +125,7 @@ __device__ __forceinline__ void pull19(const double *__restrict__ ps, const uint
     if (MASK && q > 0) {
       if (ms[d - cz(q) * g.plane]) src = bounce(q) * g.plane;
     }
-    f[q] = __ldg(ps + src);
+    f[q] = load_pop<POL>(ps + src, pol);
   }
 }
 

@@ -6,6 +6,7 @@
 #include "step_two_pass.cuh"
 #include "step_zmarch.cuh"
 #include "step_zpipe.cuh"
+#include "step_wave.cuh"
 #include <cstdlib>
 
 namespace dlbc {
@@ -169,6 +170,72 @@ cudaError_t DLBC_MODE_NAME(launch_zpipe)(const StepLaunch &L, int z_begin, int z
   (void)z_begin;
   return cudaErrorNotSupported;
 #endif
+}
+
+// ---- L2-ordered single launch (step_wave.cuh) ----
+template <int C, int EQ, int PSI, bool MASK>
+static cudaError_t wave_launch(const StepLaunch &L, int z_begin, int z_count) {
+  static const char *e_tyb = std::getenv("DLBC_WAVE_TYB");
+  static const char *e_la = std::getenv("DLBC_WAVE_LA");
+  const Geom &g = L.g;
+  if (g.periodic_z_local && !(z_begin == 1 && z_count == g.nz)) return cudaErrorInvalidValue;
+  Wave w;
+  w.z_begin = z_begin;
+  w.z_end = z_begin + z_count;
+  w.pre = g.periodic_z_local ? 1 : 0;
+  w.pl = g.periodic_z_local ? 1 : (z_begin - 1 < 1 ? 1 : z_begin - 1);
+  w.ph = g.periodic_z_local ? g.nz - 1 : (w.z_end > g.nz ? g.nz : w.z_end);
+  // band-plane of ~16k sites (5 MB of populations at C = 2): measured best on 512^2 planes (profiles/README.md)
+  w.tyb = e_tyb ? std::atoi(e_tyb) : (int)(16384 / g.nx);
+  if (w.tyb < 8) w.tyb = 8;
+  if (w.tyb > g.ny) w.tyb = g.ny;
+  w.xb = (g.nx + WAVE_SEG - 1) / WAVE_SEG;
+  // lag of F behind P: at least 2 slots (F(z) reads psi(z+1)); more when a band-plane is smaller than
+  // the ~80k sites the GPU keeps in flight, so that F blocks rarely have to wait
+  int la = e_la ? std::atoi(e_la) : (int)((65536 + (int64_t)w.tyb * g.nx - 1) / ((int64_t)w.tyb * g.nx));
+  if (la < 2) la = 2;
+  if (!e_la && la > 8) la = 8;
+  w.la = la;
+  w.rp = (w.tyb + 2) * w.xb;
+  w.rf = w.tyb * w.xb;
+  const int np = w.ph - w.pl + 1, nf = z_count + w.la;
+  w.slots = 1 + (np > nf ? np : nf);
+  w.nbands = (g.ny + w.tyb - 1) / w.tyb;
+  w.sync = L.wave_sync;
+  if (!w.sync) return cudaErrorInvalidValue;
+  const int64_t blocks = (int64_t)w.nbands * w.slots * (w.rp + w.rf);
+  if (blocks >= ((int64_t)1 << 31)) return cudaErrorInvalidConfiguration;
+  cudaError_t e = cudaMemsetAsync(w.sync, 0, wave_sync_ints(g, w.tyb) * sizeof(int), L.stream);
+  if (e != cudaSuccess) return e;
+  // persistent grid: as many blocks as can be resident (fewer when the launch is small)
+  static int resident = 0;
+  if (!resident) {
+    int dev = 0, sms = 0, per_sm = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wave_kernel<C, EQ, PSI, MASK, kExact>, WAVE_SEG, 0);
+    resident = sms * (per_sm > 0 ? per_sm : 1);
+  }
+  const unsigned grid = (unsigned)(blocks < resident ? blocks : resident);
+  wave_kernel<C, EQ, PSI, MASK, kExact><<<grid, WAVE_SEG, 0, L.stream>>>(g, L.f, L.p, w);
+  return cudaGetLastError();
+}
+
+template <int C, int EQ>
+static cudaError_t wave_eq(const StepLaunch &L, int z_begin, int z_count) {
+  if (L.psi == 0) return L.mask ? wave_launch<C, EQ, 0, true>(L, z_begin, z_count) : wave_launch<C, EQ, 0, false>(L, z_begin, z_count);
+  return L.mask ? wave_launch<C, EQ, 1, true>(L, z_begin, z_count) : wave_launch<C, EQ, 1, false>(L, z_begin, z_count);
+}
+
+cudaError_t DLBC_MODE_NAME(launch_wave)(const StepLaunch &L, int z_begin, int z_count) {
+  if (z_count <= 0) return cudaSuccess;
+  if (!L.sc) return cudaErrorNotSupported;
+  switch (L.eq) {
+    case 0: return wave_eq<DLBC_NC, 0>(L, z_begin, z_count);
+    case 1: return wave_eq<DLBC_NC, 1>(L, z_begin, z_count);
+    case 2: return wave_eq<DLBC_NC, 2>(L, z_begin, z_count);
+    default: return cudaErrorInvalidValue;
+  }
 }
 
 }  // namespace dlbc

@@ -20,12 +20,9 @@
 namespace dlbc {
 
 // ---- K1 -------------------------------------------------------------------------------------
-template <int C, int PSI, bool MASK>
-__global__ void __launch_bounds__(128) psi_kernel(Geom g, Fields fl, int z_begin) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  if (x >= g.nx) return;
-  const int y = blockIdx.y;
-  const int zg = z_begin + blockIdx.z;  // ghost-inclusive plane index, 1..nz
+// psi of all components at one site of ghost-inclusive plane zg (and its periodic ghost copies)
+template <int C, int PSI, bool MASK, int POL = POL_DEFAULT>
+__device__ __forceinline__ void psi_site(const Geom &g, const Fields &fl, int x, int y, int zg) {
   const Nbr n = make_nbr(g, x, y);
   const uint8_t *ms = mask_plane(fl.mask, g, zg) + n.sxy;
   if (MASK && ms[0]) return;  // psi of solid sites is never read (force.d:273 uses the own-site psi)
@@ -33,7 +30,7 @@ __global__ void __launch_bounds__(128) psi_kernel(Geom g, Fields fl, int z_begin
 #pragma unroll
   for (int c = 0; c < C; c++) {
     double f[Q];
-    pull19<MASK>(ps + c * g.fc, ms, g, n, f);
+    pull19<MASK, POL>(ps + c * g.fc, ms, g, n, f);
     const double v = psi_of<PSI>(density19(f));
     psi_plane(fl.psi, g, zg, c)[n.sxy] = v;
     if (g.periodic_z_local) {
@@ -43,19 +40,28 @@ __global__ void __launch_bounds__(128) psi_kernel(Geom g, Fields fl, int z_begin
   }
 }
 
+template <int C, int PSI, bool MASK>
+__global__ void __launch_bounds__(128) psi_kernel(Geom g, Fields fl, int z_begin) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= g.nx) return;
+  psi_site<C, PSI, MASK>(g, fl, x, blockIdx.y, z_begin + blockIdx.z);  // ghost-inclusive plane index, 1..nz
+}
+
 // ---- Shan-Chen force for all components of one site (force.d:238-309) -----------------------
 // Accumulation order per component f1 is the reference's: f2 outer, q = 1..18 inner, then the
 // wall term q = 0..18; prefactor = ((w_q * psi1) * psi2) * cc.
-template <int C, bool MASK, bool EXACT>
+// COHERENT: psi was written by other blocks of the SAME launch (step_wave.cuh): ordinary loads
+// instead of the read-only (ld.global.nc) path.
+template <int C, bool MASK, bool EXACT, bool COHERENT = false>
 __device__ __forceinline__ void shan_chen_force(const Geom &g, const Fields &fl, const StepParams &P, int zg,
                                                 const Nbr &n, const double (&psi1)[C], double (&F)[C][3]) {
   const uint8_t *ms = mask_plane(fl.mask, g, zg) + n.sxy;
-  const double *__restrict__ pp = psi_plane(fl.psi, g, zg, 0) + n.sxy;
+  const double *pp = psi_plane(fl.psi, g, zg, 0) + n.sxy;  // not __restrict__: see COHERENT
   const int64_t cstride = g.sites_g;
   sc_force<C, EXACT>(P, psi1, F, [&](int f2, int q) -> double {
     const int d = n.ox[1 + cx(q)] + n.oy[1 + cy(q)] + cz(q) * g.plane;
     if (MASK && ms[d]) return psi1[f2];
-    return __ldg(pp + f2 * cstride + d);
+    return COHERENT ? pp[f2 * cstride + d] : __ldg(pp + f2 * cstride + d);
   });
 }
 
@@ -109,11 +115,13 @@ __device__ __forceinline__ void common_velocity(const StepParams &P, const doubl
 // Store one component's post-collision populations of site (plane zg, sxy) and, when the slab is
 // its own z neighbour, fill next step's ghost planes with the populations that will cross the
 // periodic boundary (only c_z = +1 upward, c_z = -1 downward).
+template <int POL = POL_DEFAULT>
 __device__ __forceinline__ void store19(const Geom &g, double *__restrict__ f_new, int zg, int c, int sxy,
                                         const double (&f)[Q]) {
   double *__restrict__ out = f_plane(f_new, g, zg, c) + sxy;
+  const uint64_t pol = make_policy<POL>();
 #pragma unroll
-  for (int q = 0; q < Q; q++) out[q * g.plane] = f[q];
+  for (int q = 0; q < Q; q++) store_pop<POL>(out + q * g.plane, f[q], pol);
   if (g.periodic_z_local) {
     if (zg == g.nz) {
       double *__restrict__ gh = f_plane(f_new, g, 0, c) + sxy;
@@ -128,12 +136,8 @@ __device__ __forceinline__ void store19(const Geom &g, double *__restrict__ f_ne
   }
 }
 
-template <int C, int EQ, bool SC, bool MASK, bool EXACT>
-__global__ void __launch_bounds__(128, (MASK && SC) ? 3 : 4) fused_kernel(Geom g, Fields fl, StepParams P, int z_begin) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  if (x >= g.nx) return;
-  const int y = blockIdx.y;
-  const int zg = z_begin + blockIdx.z;
+template <int C, int EQ, bool SC, bool MASK, bool EXACT, bool COHERENT = false, int POL = POL_DEFAULT>
+__device__ __forceinline__ void fused_site(const Geom &g, const Fields &fl, const StepParams &P, int x, int y, int zg) {
   const Nbr n = make_nbr(g, x, y);
   const uint8_t *ms = mask_plane(fl.mask, g, zg) + n.sxy;
   // Solid sites: advection copies them (advection.d:83-85) and they never collide; both
@@ -144,7 +148,7 @@ __global__ void __launch_bounds__(128, (MASK && SC) ? 3 : 4) fused_kernel(Geom g
   const double *ps = f_plane(fl.f_old, g, zg, 0) + n.sxy;
 #pragma unroll
   for (int c = 0; c < C; c++) {
-    pull19<MASK>(ps + c * g.fc, ms, g, n, f[c]);
+    pull19<MASK, POL>(ps + c * g.fc, ms, g, n, f[c]);
     rho[c] = density19(f[c]);
     momentum19(f[c], m[c]);
     F[c][0] = 0.0; F[c][1] = 0.0; F[c][2] = 0.0;
@@ -153,7 +157,7 @@ __global__ void __launch_bounds__(128, (MASK && SC) ? 3 : 4) fused_kernel(Geom g
     double psi1[C];
 #pragma unroll
     for (int c = 0; c < C; c++) psi1[c] = psi_plane(fl.psi, g, zg, c)[n.sxy];
-    shan_chen_force<C, MASK, EXACT>(g, fl, P, zg, n, psi1, F);
+    shan_chen_force<C, MASK, EXACT, COHERENT>(g, fl, P, zg, n, psi1, F);
     if (MASK && P.any_gwc) wall_force<C>(g, fl, P, zg, n, psi1, F);
   }
   double u[3] = {0.0, 0.0, 0.0};
@@ -161,8 +165,15 @@ __global__ void __launch_bounds__(128, (MASK && SC) ? 3 : 4) fused_kernel(Geom g
 #pragma unroll
   for (int c = 0; c < C; c++) {
     collide_site<EQ, EXACT>(f[c], rho[c], m[c], F[c], u, P, c);
-    store19(g, fl.f_new, zg, c, n.sxy, f[c]);
+    store19<POL>(g, fl.f_new, zg, c, n.sxy, f[c]);
   }
+}
+
+template <int C, int EQ, bool SC, bool MASK, bool EXACT>
+__global__ void __launch_bounds__(128, (MASK && SC) ? 3 : 4) fused_kernel(Geom g, Fields fl, StepParams P, int z_begin) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= g.nx) return;
+  fused_site<C, EQ, SC, MASK, EXACT>(g, fl, P, x, blockIdx.y, z_begin + blockIdx.z);
 }
 
 // ---- L.force[comp] for output (lb/io.d:86-90) -----------------------------------------------

@@ -18,7 +18,7 @@ ABI_VERSION = 1
 PSI = {"Linear": 0, "Exponential": 1}
 EQ = {"SecondOrder": 0, "ThirdOrder": 1, "BDist2": 2}
 ARITH = {"fast": 0, "exact": 1}
-KERNEL = {"auto": 0, "two_pass": 1, "zmarch": 2, "zpipe": 3}
+KERNEL = {"auto": 0, "two_pass": 1, "zmarch": 2, "zpipe": 3, "wave": 4}
 
 # every symbol include/dlbc_cuda.h declares (tests check that the library exports all of them)
 SYMBOLS = [

@@ -56,8 +56,10 @@ enum {
   DLBC_KERNEL_AUTO = 0,
   DLBC_KERNEL_TWO_PASS = 1,   /* psi kernel + fused pull/force/collide kernel (psi via L1/L2) */
   DLBC_KERNEL_ZMARCH = 2,     /* single pass: z-marching fused kernel, psi planes in shared memory */
-  DLBC_KERNEL_ZPIPE = 3       /* single pass: z-march with the population loads as an asynchronous
+  DLBC_KERNEL_ZPIPE = 3,      /* single pass: z-march with the population loads as an asynchronous
                                  cp.async shared-memory pipeline (loads of plane z+2 overlap plane z) */
+  DLBC_KERNEL_WAVE = 4        /* psi sites + fused sites in ONE launch, ticket-ordered band by band so
+                                 that the second gather of every population is an L2 hit */
 };
 
 /* Replaces: the module-level parameters the timestep reads -- lattice.gn (lattice.d:28),

@@ -17,7 +17,7 @@ from dlbc_b200.connectivity import d3q19  # noqa: E402
 from dlbc_b200.lattice import Lattice  # noqa: E402
 from oracle import oracle as O  # noqa: E402
 
-KERNELS = ["two_pass", "zmarch", "zpipe"]
+KERNELS = ["two_pass", "zmarch", "zpipe", "wave"]
 
 
 def make_pair(params, pops, mask, **gpu_kw):
