@@ -526,7 +526,10 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
   }
   for (int d = 0; d < 3; d++) p.gacc[d] = cfg->global_acc[d];
 
-  ctx->variant = cfg->kernel_variant == DLBC_KERNEL_AUTO ? DLBC_KERNEL_TWO_PASS : cfg->kernel_variant;
+  // AUTO: the L2-ordered single launch on one GPU (fastest measured, profiles/README.md); the two-kernel
+  // schedule on z-slabs, where its boundary/interior split overlaps both exchanges with compute
+  ctx->variant = cfg->kernel_variant != DLBC_KERNEL_AUTO ? cfg->kernel_variant
+                 : (cfg->nranks == 1 ? DLBC_KERNEL_WAVE : DLBC_KERNEL_TWO_PASS);
   if (!cfg->enable_shan_chen) ctx->variant = DLBC_KERNEL_TWO_PASS;
   if (cfg->nranks > 1 && ctx->variant == DLBC_KERNEL_ZMARCH) ctx->variant = DLBC_KERNEL_TWO_PASS;  // no ghost-psi path
   if (cfg->ncomp > 2 && ctx->variant != DLBC_KERNEL_WAVE)

@@ -72,11 +72,16 @@ template <int C, int EQ, int PSI, bool MASK, int TX, int TY, int MINB>
 static cudaError_t zmarch_launch(const StepLaunch &L, int z_begin, int z_count, int chunk) {
   auto kern = zmarch_kernel<C, EQ, PSI, MASK, kExact, TX, TY, MINB>;
   constexpr size_t smem = (size_t)(C * Q * TX * TY + 4 * C * (TX + 2) * (TY + 2)) * sizeof(double);
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    configured = true;
+  {
+    // per device (function attributes are not shared between the devices of one process)
+    static bool configured[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || !configured[dev]) {
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+      if (dev >= 0 && dev < 64) configured[dev] = true;
+    }
   }
   ZMarch zm{z_begin, z_begin + z_count, chunk};
   dim3 grid((L.g.nx + TX - 1) / TX, (L.g.ny + TY - 1) / TY, (z_count + chunk - 1) / chunk);
@@ -127,11 +132,16 @@ static cudaError_t zpipe_launch(const StepLaunch &L, int z_begin, int z_count, i
   constexpr int NT = TX * TY, NRIM = 2 * (TX + 2) + 2 * TY, RP = (TX + 2) * (TY + 2);
   constexpr size_t smem = (size_t)(2 * C * Q * NT + C * Q * NRIM + 4 * C * RP) * sizeof(double);
   static_assert(smem <= 227 * 1024, "zpipe tile does not fit in shared memory");
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    configured = true;
+  {
+    // per device (function attributes are not shared between the devices of one process)
+    static bool configured[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || !configured[dev]) {
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+      if (dev >= 0 && dev < 64) configured[dev] = true;
+    }
   }
   ZMarch zm{z_begin, z_begin + z_count, chunk};
   dim3 grid((L.g.nx + TX - 1) / TX, (L.g.ny + TY - 1) / TY, (z_count + chunk - 1) / chunk);
