@@ -265,7 +265,11 @@ def run_ours(args, rank, world, local_rank):
         if os.path.exists(tp):
             try:
                 with open(tp) as f:
-                    roof["traffic"] = json.load(f).get(dom)
+                    tr = json.load(f).get(dom)
+                    if tr:  # ncu-measured DRAM bytes per site of this kernel x the sites of one launch
+                        roof["traffic"] = tr["bytes_per_site"] * sites_local
+                        roof["traffic_bytes_per_site"] = tr["bytes_per_site"]
+                        roof["traffic_source"] = tr["source"]
             except Exception:
                 pass
     else:

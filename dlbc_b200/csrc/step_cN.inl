@@ -187,6 +187,8 @@ template <int C, int EQ, int PSI, bool MASK>
 static cudaError_t wave_launch(const StepLaunch &L, int z_begin, int z_count) {
   static const char *e_tyb = std::getenv("DLBC_WAVE_TYB");
   static const char *e_la = std::getenv("DLBC_WAVE_LA");
+  static const char *e_pf = std::getenv("DLBC_WAVE_PF");      // prefetch distance in tickets (0 = off = default)
+  static const char *e_pfk = std::getenv("DLBC_WAVE_PFKEEP"); // 1 (default): prefetch with L2::evict_last
   const Geom &g = L.g;
   if (g.periodic_z_local && !(z_begin == 1 && z_count == g.nz)) return cudaErrorInvalidValue;
   Wave w;
@@ -227,6 +229,10 @@ static cudaError_t wave_launch(const StepLaunch &L, int z_begin, int z_count) {
     resident = sms * (per_sm > 0 ? per_sm : 1);
   }
   const unsigned grid = (unsigned)(blocks < resident ? blocks : resident);
+  w.pf = e_pf ? std::atoi(e_pf) : 0;   // measured slower when on (profiles/r01_wave_experiments.md): L2 capacity, not latency, is the limit
+  w.pf_keep = e_pfk ? std::atoi(e_pfk) : 1;
+  static const char *e_batch = std::getenv("DLBC_WAVE_BATCH");
+  w.batch = e_batch ? std::atoi(e_batch) : 0;
   wave_kernel<C, EQ, PSI, MASK, kExact><<<grid, WAVE_SEG, 0, L.stream>>>(g, L.f, L.p, w);
   return cudaGetLastError();
 }

@@ -21,21 +21,36 @@ namespace dlbc {
 
 // ---- K1 -------------------------------------------------------------------------------------
 // psi of all components at one site of ghost-inclusive plane zg (and its periodic ghost copies)
-template <int C, int PSI, bool MASK, int POL = POL_DEFAULT>
+// BATCH: gather the populations of ALL components before the first sum, so that C*19 loads are in
+// flight per thread instead of 19 (the wave variant runs its psi items at 16 warps/SM, where the
+// serial form spent two full memory latencies per site: profiles/r01_wave_before.md).
+template <int C, int PSI, bool MASK, int POL = POL_DEFAULT, bool BATCH = false>
 __device__ __forceinline__ void psi_site(const Geom &g, const Fields &fl, int x, int y, int zg) {
   const Nbr n = make_nbr(g, x, y);
   const uint8_t *ms = mask_plane(fl.mask, g, zg) + n.sxy;
   if (MASK && ms[0]) return;  // psi of solid sites is never read (force.d:273 uses the own-site psi)
   const double *ps = f_plane(fl.f_old, g, zg, 0) + n.sxy;
+  double v[C];
+  if (BATCH) {
+    double f[C][Q];
+#pragma unroll
+    for (int c = 0; c < C; c++) pull19<MASK, POL>(ps + c * g.fc, ms, g, n, f[c]);
+#pragma unroll
+    for (int c = 0; c < C; c++) v[c] = psi_of<PSI>(density19(f[c]));
+  } else {
+#pragma unroll
+    for (int c = 0; c < C; c++) {
+      double f[Q];
+      pull19<MASK, POL>(ps + c * g.fc, ms, g, n, f);
+      v[c] = psi_of<PSI>(density19(f));
+    }
+  }
 #pragma unroll
   for (int c = 0; c < C; c++) {
-    double f[Q];
-    pull19<MASK, POL>(ps + c * g.fc, ms, g, n, f);
-    const double v = psi_of<PSI>(density19(f));
-    psi_plane(fl.psi, g, zg, c)[n.sxy] = v;
+    psi_plane(fl.psi, g, zg, c)[n.sxy] = v[c];
     if (g.periodic_z_local) {
-      if (zg == g.nz) psi_plane(fl.psi, g, 0, c)[n.sxy] = v;         // -> ghost plane 0
-      if (zg == 1) psi_plane(fl.psi, g, g.nz + 1, c)[n.sxy] = v;     // -> ghost plane nz+1
+      if (zg == g.nz) psi_plane(fl.psi, g, 0, c)[n.sxy] = v[c];         // -> ghost plane 0
+      if (zg == 1) psi_plane(fl.psi, g, g.nz + 1, c)[n.sxy] = v[c];     // -> ghost plane nz+1
     }
   }
 }

@@ -40,6 +40,9 @@ struct Wave {
   int rp, rf;          // P / F blocks per slot: (tyb + 2) * xb, tyb * xb
   int slots;           // slots per band
   int nbands;
+  int pf;              // L2 prefetch distance in tickets (0 = off): see wave_prefetch
+  int pf_keep;         // prefetch with L2::evict_last (else default priority)
+  int batch;           // P items gather all components before summing (psi_site BATCH)
   int *sync;           // [0] ticket, [1 + band * (nz + 2) + plane] completed P blocks
 };
 
@@ -58,6 +61,61 @@ __device__ __forceinline__ void red_release_add(int *p, int v) {
   asm volatile("red.release.gpu.global.add.s32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
 }
 
+constexpr int WAVE_SEG = 128;  // sites per item == threads per block
+#ifndef WAVE_PREFETCH
+#define WAVE_PREFETCH true
+#endif
+
+// c_y / c_z of a run-time q (the constexpr tables of lb_site.cuh are for unrolled loops): 2-bit codes
+__host__ __device__ constexpr uint64_t pack_codes(int (*fn)(int)) {
+  uint64_t m = 0;
+  for (int q = 0; q < Q; q++) m |= (uint64_t)(fn(q) + 1) << (2 * q);
+  return m;
+}
+__device__ __forceinline__ int cy_rt(int q) { constexpr uint64_t m = pack_codes(cy); return (int)((m >> (2 * q)) & 3) - 1; }
+__device__ __forceinline__ int cz_rt(int q) { constexpr uint64_t m = pack_codes(cz); return (int)((m >> (2 * q)) & 3) - 1; }
+
+// DRAM -> L2 prefetch of everything the P item with ticket tp will gather: C*19 row segments of
+// WAVE_SEG doubles, one prefetch per 128-byte line, spread over the block's threads.  A P item is
+// pure streaming (38 loads, 38 adds, one exp per site) and runs at 16 warps/SM because it shares
+// the launch with the 128-register F items: without the prefetch its warps sat on two full DRAM
+// latencies per site (35 % of the kernel's warp time, profiles/r01_wave_before.md).  Issued one
+// round of tickets ahead, the prefetch costs no registers and no scoreboard, and the P item's own
+// loads then hit L2.  The x +- 1 shift of the gather stays inside the same lines except for one
+// element at either end, which belongs to the neighbouring item's segment.
+template <int C>
+__device__ __forceinline__ void wave_prefetch(const Geom &g, const Fields &fl, const Wave &w, int tp,
+                                              int per_band, int per_slot) {
+  const int band = tp / per_band;
+  const int r = tp - band * per_band;
+  const int k = r / per_slot;
+  const int j = r - k * per_slot;
+  if (j >= w.rp) return;
+  int p = -1;
+  if (k == 0) { if (w.pre) p = g.nz; }
+  else if (w.pl + (k - 1) <= w.ph) p = w.pl + (k - 1);
+  if (p < 0) return;
+  const int yb = band * w.tyb;
+  const int tb = min(w.tyb, g.ny - yb);
+  const int row = j / w.xb, xblk = j - row * w.xb;
+  if (row > tb + 1) return;
+  int y = yb - 1 + row;
+  y = y < 0 ? y + g.ny : (y >= g.ny ? y - g.ny : y);
+  const int x0 = xblk * WAVE_SEG;
+  const int lpr = (min(WAVE_SEG, g.nx - x0) + 15) >> 4;  // 128-byte lines per row segment
+  const int nlines = C * Q * lpr;
+  for (int l = threadIdx.x; l < nlines; l += WAVE_SEG) {
+    const int cq = l / lpr, s = l - cq * lpr;
+    const int c = cq / Q, q = cq - c * Q;
+    int ys = y - cy_rt(q);
+    ys = ys < 0 ? ys + g.ny : (ys >= g.ny ? ys - g.ny : ys);
+    const double *a = fl.f_old + (int64_t)(p - cz_rt(q)) * g.fz + (int64_t)c * g.fc + (int64_t)q * g.plane +
+                      ys * g.nx + x0 + s * 16;
+    if (w.pf_keep) asm volatile("prefetch.global.L2::evict_last [%0];\n" ::"l"(a));
+    else asm volatile("prefetch.global.L2 [%0];\n" ::"l"(a));
+  }
+}
+
 // Persistent 128-thread blocks (4 per SM): each block loops over tickets; an item is a 128-site row
 // segment.  The atomicAdd for the NEXT ticket is issued before the current item's work and
 // consumed after it, so its L2 round trip is hidden.  A block working on ticket t only ever waits
@@ -67,7 +125,6 @@ __device__ __forceinline__ void red_release_add(int *p, int v) {
 // (Measured alternatives, profiles/README.md: single-warp blocks with 128-site items triple the
 // number of sites in flight and overflow L2; single-warp blocks with 32-site items need a twice
 // longer lag before the F items stop waiting.  Both were slower.)
-constexpr int WAVE_SEG = 128;  // sites per item == threads per block
 
 template <int C, int EQ, int PSI, bool MASK, bool EXACT>
 __global__ void __launch_bounds__(WAVE_SEG, (MASK ? 3 : 4)) wave_kernel(Geom g, Fields fl, StepParams P, Wave w) {
@@ -81,6 +138,7 @@ __global__ void __launch_bounds__(WAVE_SEG, (MASK ? 3 : 4)) wave_kernel(Geom g, 
   for (int it = 1; t < total; it ^= 1) {
     int nxt = 0;
     if (threadIdx.x == 0) nxt = atomicAdd(w.sync, 1);  // in flight during this item's work
+    if (WAVE_PREFETCH && w.pf > 0 && t + w.pf < total) wave_prefetch<C>(g, fl, w, t + w.pf, per_band, per_slot);
 
     const int band = t / per_band;
     const int r = t - band * per_band;
@@ -101,7 +159,8 @@ __global__ void __launch_bounds__(WAVE_SEG, (MASK ? 3 : 4)) wave_kernel(Geom g, 
         if (row <= tb + 1 && x < g.nx) {
           int y = yb - 1 + row;
           y = y < 0 ? y + g.ny : (y >= g.ny ? y - g.ny : y);
-          psi_site<C, PSI, MASK, POL_KEEP>(g, fl, x, y, p);
+          if (w.batch) psi_site<C, PSI, MASK, POL_KEEP, true>(g, fl, x, y, p);
+          else psi_site<C, PSI, MASK, POL_KEEP, false>(g, fl, x, y, p);
         }
         __syncthreads();  // all psi stores of the block precede (CTA scope) thread 0's release below
         if (threadIdx.x == 0) red_release_add(cnt + p, 1);
