@@ -183,7 +183,7 @@ cudaError_t DLBC_MODE_NAME(launch_zpipe)(const StepLaunch &L, int z_begin, int z
 }
 
 // ---- L2-ordered single launch (step_wave.cuh) ----
-template <int C, int EQ, int PSI, bool MASK>
+template <int C, int EQ, int PSI, bool MASK, bool SPLIT>
 static cudaError_t wave_launch(const StepLaunch &L, int z_begin, int z_count) {
   static const char *e_tyb = std::getenv("DLBC_WAVE_TYB");
   static const char *e_la = std::getenv("DLBC_WAVE_LA");
@@ -225,7 +225,7 @@ static cudaError_t wave_launch(const StepLaunch &L, int z_begin, int z_count) {
     int dev = 0, sms = 0, per_sm = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wave_kernel<C, EQ, PSI, MASK, kExact>, WAVE_SEG, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wave_kernel<C, EQ, PSI, MASK, kExact, SPLIT>, WAVE_SEG * (SPLIT ? C : 1), 0);
     resident = sms * (per_sm > 0 ? per_sm : 1);
   }
   const unsigned grid = (unsigned)(blocks < resident ? blocks : resident);
@@ -233,14 +233,24 @@ static cudaError_t wave_launch(const StepLaunch &L, int z_begin, int z_count) {
   w.pf_keep = e_pfk ? std::atoi(e_pfk) : 1;
   static const char *e_batch = std::getenv("DLBC_WAVE_BATCH");
   w.batch = e_batch ? std::atoi(e_batch) : 0;
-  wave_kernel<C, EQ, PSI, MASK, kExact><<<grid, WAVE_SEG, 0, L.stream>>>(g, L.f, L.p, w);
+  wave_kernel<C, EQ, PSI, MASK, kExact, SPLIT><<<grid, dim3(WAVE_SEG, SPLIT ? C : 1), 0, L.stream>>>(g, L.f, L.p, w);
   return cudaGetLastError();
+}
+
+template <int C, int EQ, bool SPLIT>
+static cudaError_t wave_psi(const StepLaunch &L, int z_begin, int z_count) {
+  if (L.psi == 0) return L.mask ? wave_launch<C, EQ, 0, true, SPLIT>(L, z_begin, z_count) : wave_launch<C, EQ, 0, false, SPLIT>(L, z_begin, z_count);
+  return L.mask ? wave_launch<C, EQ, 1, true, SPLIT>(L, z_begin, z_count) : wave_launch<C, EQ, 1, false, SPLIT>(L, z_begin, z_count);
 }
 
 template <int C, int EQ>
 static cudaError_t wave_eq(const StepLaunch &L, int z_begin, int z_count) {
-  if (L.psi == 0) return L.mask ? wave_launch<C, EQ, 0, true>(L, z_begin, z_count) : wave_launch<C, EQ, 0, false>(L, z_begin, z_count);
-  return L.mask ? wave_launch<C, EQ, 1, true>(L, z_begin, z_count) : wave_launch<C, EQ, 1, false>(L, z_begin, z_count);
+  // DLBC_WAVE_SPLIT=1 selects the one-thread-per-(site, component) form (step_wave.cuh); measured
+  // slower than one thread per site (profiles/README.md), so it is off by default
+  static const char *e_split = std::getenv("DLBC_WAVE_SPLIT");
+  const bool split = C > 1 && (e_split ? std::atoi(e_split) != 0 : false);
+  if constexpr (C > 1) { if (split) return wave_psi<C, EQ, true>(L, z_begin, z_count); }
+  return wave_psi<C, EQ, false>(L, z_begin, z_count);
 }
 
 cudaError_t DLBC_MODE_NAME(launch_wave)(const StepLaunch &L, int z_begin, int z_count) {

@@ -116,6 +116,151 @@ __device__ __forceinline__ void wave_prefetch(const Geom &g, const Fields &fl, c
   }
 }
 
+// ---- component-split site functions -----------------------------------------------------------
+// One thread per (site, component) instead of one thread per site.  Why: a thread that owns all
+// C components of a site holds 19 C populations (76 registers at C = 2), which pins the launch at
+// 128 registers = 16 warps/SM, and the GPU then needs ~75k sites in flight to cover memory
+// latency -- 46 MB of populations, which together with the P -> F lag overflows what L2 retains
+// (profiles/r01_wave_experiments.md: every change that made the P items faster RAISED the DRAM
+// traffic).  Split by component, a thread holds 19 populations, the launch fits 24+ warps/SM with
+// fewer sites in flight, and the only cross-component coupling of the timestep -- BDist2's common
+// velocity (collision.d:156-196) -- goes through 4 doubles per thread of shared memory.  A warp is
+// uniform in its component (threadIdx.y), so every load/store is still a full 256-byte row piece.
+// Per-site arithmetic is the same sequence of operations as fused_site/psi_site: identical bits.
+
+// sc_force (lb_site.cuh) for the single component f1 (run-time, warp-uniform)
+template <int C, bool EXACT, class PsiAt>
+__device__ __forceinline__ void sc_force_one(const StepParams &P, int f1, const double (&psi1)[C], double (&F)[3],
+                                             PsiAt psi_at) {
+  double p1 = psi1[0];
+#pragma unroll
+  for (int k = 1; k < C; k++) if (k == f1) p1 = psi1[k];
+#pragma unroll
+  for (int f2 = 0; f2 < C; f2++) {
+    const double cc = P.gcc[f1 * MAXC + f2];
+    if (cc == 0.0) continue;
+    if (EXACT) {
+#pragma unroll
+      for (int q = 1; q < Q; q++) {
+        const double psi2 = psi_at(f2, q);
+        const double pref = weight(q) * p1 * psi2 * cc;
+        if (cx(q) == 1) F[0] -= pref; else if (cx(q) == -1) F[0] += pref;
+        if (cy(q) == 1) F[1] -= pref; else if (cy(q) == -1) F[1] += pref;
+        if (cz(q) == 1) F[2] -= pref; else if (cz(q) == -1) F[2] += pref;
+      }
+    } else {
+      const double ax = psi_at(f2, 1) - psi_at(f2, 2);
+      const double ay = psi_at(f2, 3) - psi_at(f2, 4);
+      const double az = psi_at(f2, 5) - psi_at(f2, 6);
+      const double p7 = psi_at(f2, 7), p8 = psi_at(f2, 8), p9 = psi_at(f2, 9), p10 = psi_at(f2, 10);
+      const double p11 = psi_at(f2, 11), p12 = psi_at(f2, 12), p13 = psi_at(f2, 13), p14 = psi_at(f2, 14);
+      const double p15 = psi_at(f2, 15), p16 = psi_at(f2, 16), p17 = psi_at(f2, 17), p18 = psi_at(f2, 18);
+      const double dx = ((p7 - p8) + (p11 - p17)) + ((p12 - p18) + (p13 - p14));
+      const double dy = ((p7 - p14) + (p8 - p13)) + ((p9 - p10) + (p15 - p16));
+      const double dz = ((p9 - p15) + (p10 - p16)) + ((p11 - p12) + (p17 - p18));
+      const double w1 = weight(1), w2 = weight(7);
+      const double sx = w1 * ax + w2 * dx, sy = w1 * ay + w2 * dy, sz = w1 * az + w2 * dz;
+      const double t = p1 * cc;
+      F[0] -= t * sx;
+      F[1] -= t * sy;
+      F[2] -= t * sz;
+    }
+  }
+}
+
+// wall_force (step_two_pass.cuh) for the single component f1
+template <int C>
+__device__ __forceinline__ void wall_force_one(const Geom &g, const Fields &fl, const StepParams &P, int zg,
+                                               const Nbr &n, int f1, double p1, double (&F)[3]) {
+  const double wc = P.gwc[f1];
+  if (wc == 0.0) return;
+  const uint8_t *mp = mask_plane(fl.mask, g, zg);
+  const double *__restrict__ rw = psi_plane(fl.rho_wall, g, zg, f1);
+#pragma unroll
+  for (int q = 0; q < Q; q++) {
+    const int nb = n.at(cx(q), cy(q)) + cz(q) * g.plane;
+    if (mp[nb]) {
+      const double pref = weight(q) * p1 * rw[nb] * wc;
+      if (cx(q) == 1) F[0] -= pref; else if (cx(q) == -1) F[0] += pref;
+      if (cy(q) == 1) F[1] -= pref; else if (cy(q) == -1) F[1] += pref;
+      if (cz(q) == 1) F[2] -= pref; else if (cz(q) == -1) F[2] += pref;
+    }
+  }
+}
+
+// psi_site for component c only
+template <int C, int PSI, bool MASK, int POL>
+__device__ __forceinline__ void psi_site_split(const Geom &g, const Fields &fl, int x, int y, int zg, int c) {
+  const Nbr n = make_nbr(g, x, y);
+  const uint8_t *ms = mask_plane(fl.mask, g, zg) + n.sxy;
+  if (MASK && ms[0]) return;
+  double f[Q];
+  pull19<MASK, POL>(f_plane(fl.f_old, g, zg, c) + n.sxy, ms, g, n, f);
+  const double v = psi_of<PSI>(density19(f));
+  psi_plane(fl.psi, g, zg, c)[n.sxy] = v;
+  if (g.periodic_z_local) {
+    if (zg == g.nz) psi_plane(fl.psi, g, 0, c)[n.sxy] = v;
+    if (zg == 1) psi_plane(fl.psi, g, g.nz + 1, c)[n.sxy] = v;
+  }
+}
+
+// fused_site for component c only.  EVERY thread of the block must call it (block barrier for the
+// BDist2 exchange); in_range = false marks threads beyond the end of the row.
+// xch: shared memory [4][C][WAVE_SEG] (rho, m_x, m_y, m_z of every component of the block's sites).
+template <int C, int EQ, bool MASK, bool EXACT, int POL>
+__device__ __forceinline__ void fused_site_split(const Geom &g, const Fields &fl, const StepParams &P, int x, int y,
+                                                 int zg, int c, bool in_range, double (*xch)[C][WAVE_SEG]) {
+  const Nbr n = make_nbr(g, in_range ? x : 0, y);
+  const uint8_t *ms = mask_plane(fl.mask, g, zg) + n.sxy;
+  const bool act = in_range && !(MASK && ms[0]);
+  double f[Q], rho = 0.0, m[3] = {0.0, 0.0, 0.0}, F[3] = {0.0, 0.0, 0.0};
+  if (act) {
+    pull19<MASK, POL>(f_plane(fl.f_old, g, zg, c) + n.sxy, ms, g, n, f);
+    rho = density19(f);
+    momentum19(f, m);
+    double psi1[C];
+#pragma unroll
+    for (int k = 0; k < C; k++) psi1[k] = psi_plane(fl.psi, g, zg, k)[n.sxy];
+    const double *pp = psi_plane(fl.psi, g, zg, 0) + n.sxy;  // written by P items of this launch: plain loads
+    const int64_t cstride = g.sites_g;
+    sc_force_one<C, EXACT>(P, c, psi1, F, [&](int f2, int q) -> double {
+      const int d = n.ox[1 + cx(q)] + n.oy[1 + cy(q)] + cz(q) * g.plane;
+      if (MASK && ms[d]) return psi1[f2];
+      return pp[f2 * cstride + d];
+    });
+    if (MASK && P.any_gwc) {
+      double p1 = psi1[0];
+#pragma unroll
+      for (int k = 1; k < C; k++) if (k == c) p1 = psi1[k];
+      wall_force_one<C>(g, fl, P, zg, n, c, p1, F);
+    }
+  }
+  double u[3] = {0.0, 0.0, 0.0};
+  if (EQ == 2) {
+    const int tx = threadIdx.x;
+    xch[0][c][tx] = rho;
+    xch[1][c][tx] = m[0];
+    xch[2][c][tx] = m[1];
+    xch[3][c][tx] = m[2];
+    __syncthreads();
+    if (act) {
+      double ra[C], ma[C][3];
+#pragma unroll
+      for (int k = 0; k < C; k++) {
+        ra[k] = xch[0][k][tx];
+        ma[k][0] = xch[1][k][tx];
+        ma[k][1] = xch[2][k][tx];
+        ma[k][2] = xch[3][k][tx];
+      }
+      common_velocity<C, EXACT>(P, ma, ra, u);
+    }
+  }
+  if (act) {
+    collide_site<EQ, EXACT>(f, rho, m, F, u, P, c);
+    store19<POL>(g, fl.f_new, zg, c, n.sxy, f);
+  }
+}
+
 // Persistent 128-thread blocks (4 per SM): each block loops over tickets; an item is a 128-site row
 // segment.  The atomicAdd for the NEXT ticket is issued before the current item's work and
 // consumed after it, so its L2 round trip is hidden.  A block working on ticket t only ever waits
@@ -126,19 +271,27 @@ __device__ __forceinline__ void wave_prefetch(const Geom &g, const Fields &fl, c
 // number of sites in flight and overflow L2; single-warp blocks with 32-site items need a twice
 // longer lag before the F items stop waiting.  Both were slower.)
 
-template <int C, int EQ, int PSI, bool MASK, bool EXACT>
-__global__ void __launch_bounds__(WAVE_SEG, (MASK ? 3 : 4)) wave_kernel(Geom g, Fields fl, StepParams P, Wave w) {
+// SPLIT: block = WAVE_SEG sites x C components (threadIdx.y = component), see above.
+template <int C, bool MASK, bool SPLIT>
+constexpr int wave_min_blocks() { return !SPLIT ? (MASK ? 3 : 4) : (C <= 2 ? 3 : (C == 3 ? 2 : 1)); }
+
+template <int C, int EQ, int PSI, bool MASK, bool EXACT, bool SPLIT>
+__global__ void __launch_bounds__(WAVE_SEG * (SPLIT ? C : 1), (wave_min_blocks<C, MASK, SPLIT>()))
+wave_kernel(Geom g, Fields fl, StepParams P, Wave w) {
   __shared__ int s_ticket[2];
+  __shared__ double s_xch[SPLIT ? 4 : 1][SPLIT ? C : 1][SPLIT ? WAVE_SEG : 1];
+  const int comp = SPLIT ? (int)threadIdx.y : 0;
+  const bool lead = threadIdx.x == 0 && comp == 0;
   const int per_slot = w.rp + w.rf;
   const int per_band = w.slots * per_slot;
   const int total = w.nbands * per_band;
-  if (threadIdx.x == 0) s_ticket[0] = atomicAdd(w.sync, 1);
+  if (lead) s_ticket[0] = atomicAdd(w.sync, 1);
   __syncthreads();
   int t = s_ticket[0];
   for (int it = 1; t < total; it ^= 1) {
     int nxt = 0;
-    if (threadIdx.x == 0) nxt = atomicAdd(w.sync, 1);  // in flight during this item's work
-    if (WAVE_PREFETCH && w.pf > 0 && t + w.pf < total) wave_prefetch<C>(g, fl, w, t + w.pf, per_band, per_slot);
+    if (lead) nxt = atomicAdd(w.sync, 1);  // in flight during this item's work
+    if (WAVE_PREFETCH && !SPLIT && w.pf > 0 && t + w.pf < total) wave_prefetch<C>(g, fl, w, t + w.pf, per_band, per_slot);
 
     const int band = t / per_band;
     const int r = t - band * per_band;
@@ -159,11 +312,12 @@ __global__ void __launch_bounds__(WAVE_SEG, (MASK ? 3 : 4)) wave_kernel(Geom g, 
         if (row <= tb + 1 && x < g.nx) {
           int y = yb - 1 + row;
           y = y < 0 ? y + g.ny : (y >= g.ny ? y - g.ny : y);
-          if (w.batch) psi_site<C, PSI, MASK, POL_KEEP, true>(g, fl, x, y, p);
+          if constexpr (SPLIT) psi_site_split<C, PSI, MASK, POL_KEEP>(g, fl, x, y, p, comp);
+          else if (w.batch) psi_site<C, PSI, MASK, POL_KEEP, true>(g, fl, x, y, p);
           else psi_site<C, PSI, MASK, POL_KEEP, false>(g, fl, x, y, p);
         }
-        __syncthreads();  // all psi stores of the block precede (CTA scope) thread 0's release below
-        if (threadIdx.x == 0) red_release_add(cnt + p, 1);
+        __syncthreads();  // all psi stores of the block precede (CTA scope) the lead thread's release below
+        if (lead) red_release_add(cnt + p, 1);
       }
     } else if (k > 0) {
       // ---- F item: fused update of one row segment of plane zf
@@ -171,7 +325,7 @@ __global__ void __launch_bounds__(WAVE_SEG, (MASK ? 3 : 4)) wave_kernel(Geom g, 
       const int jf = j - w.rp;
       const int row = jf / w.xb, xblk = jf - row * w.xb;
       if (zf >= w.z_begin && zf < w.z_end && row < tb) {
-        if (threadIdx.x < 3) {
+        if (threadIdx.x < 3 && comp == 0) {
           int d = zf + (int)threadIdx.x - 1;
           bool need = true;
           if (d < 1) { need = g.periodic_z_local; d = g.nz; }
@@ -183,11 +337,12 @@ __global__ void __launch_bounds__(WAVE_SEG, (MASK ? 3 : 4)) wave_kernel(Geom g, 
         }
         __syncthreads();
         const int x = xblk * WAVE_SEG + threadIdx.x;
-        if (x < g.nx) fused_site<C, EQ, true, MASK, EXACT, true, POL_STREAM>(g, fl, P, x, yb + row, zf);
+        if constexpr (SPLIT) fused_site_split<C, EQ, MASK, EXACT, POL_STREAM>(g, fl, P, x, yb + row, zf, comp, x < g.nx, s_xch);
+        else if (x < g.nx) fused_site<C, EQ, true, MASK, EXACT, true, POL_STREAM>(g, fl, P, x, yb + row, zf);
       }
     }
 
-    if (threadIdx.x == 0) s_ticket[it] = nxt;
+    if (lead) s_ticket[it] = nxt;
     __syncthreads();
     t = s_ticket[it];
   }
