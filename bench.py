@@ -184,11 +184,8 @@ def run_ours(args, rank, world, local_rank):
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-        idt = torch.zeros(dlib.NCCL_ID_BYTES, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            idt.copy_(torch.frombuffer(bytearray(dlib.nccl_unique_id()), dtype=torch.uint8))
-        dist.broadcast(idt, 0)
-        nccl_id = bytes(idt.cpu().numpy().tobytes())
+        from dlbc_b200 import slabs
+        nccl_id = slabs.broadcast_unique_id(dist, rank, dlib.nccl_unique_id, dlib.NCCL_ID_BYTES, device="cuda")
 
     n = args.size
     ncomp = args.components
@@ -225,10 +222,8 @@ def run_ours(args, rank, world, local_rank):
     def max_over_ranks(x):
         if dist is None:
             return x
-        import torch
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+        from dlbc_b200 import slabs
+        return slabs.max_over_ranks(dist, x, device="cuda")
 
     # ---- device-resident timing: W warm-up steps, then exactly K timed steps ----
     G.step(args.warmup)
