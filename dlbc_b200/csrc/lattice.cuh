@@ -84,6 +84,49 @@ __device__ __forceinline__ double *psi_plane(double *p, const Geom &g, int zg, i
 // (advectable) site: f[q] = bounce-back(mask[p - c_q]) ? old[p][bounce q] : old[p - c_q][q].
 // ps = f_plane(f_old, g, zg, c) + n.sxy  (per-thread pointer to the site's q = 0 entry: every
 // access is then ps[int offset], one IMAD.WIDE), ms = mask_plane(mask, g, zg) + n.sxy.
+// base + off elements as ONE IMAD.WIDE.  Written as PTX because nvcc otherwise folds the per-thread base
+// pointer back into (block base + 64-bit site index) and rebuilds every address from a sign-extended
+// 64-bit index sum: shift, add, add-with-carry, LEA, LEA.HI.X -- 5-6 integer instructions per load, ~45 %
+// of the fused path's instruction stream (profiles/README.md).  All offsets a site update needs lie within
+// +-1 plane block of its own entry, hence 32 bits (see Geom).
+#ifndef DLBC_WIDE_STANDALONE
+#define DLBC_WIDE_STANDALONE 1
+#endif
+__device__ __forceinline__ const double *ptr_at(const double *base, int off) {
+  const double *r;
+  asm("mad.wide.s32 %0, %1, 8, %2;" : "=l"(r) : "r"(off), "l"(base));
+  return r;
+}
+__device__ __forceinline__ double *ptr_at(double *base, int off) {
+  double *r;
+  asm("mad.wide.s32 %0, %1, 8, %2;" : "=l"(r) : "r"(off), "l"(base));
+  return r;
+}
+__device__ __forceinline__ const uint8_t *ptr_at(const uint8_t *base, int off) {
+  const uint8_t *r;
+  asm("mad.wide.s32 %0, %1, 1, %2;" : "=l"(r) : "r"(off), "l"(base));
+  return r;
+}
+
+// Loads through a ptr_at() address: the address-space inference is lost across the asm, so say .global
+// explicitly (a generic LD costs an extra address-space check).  ld_global is the ordinary coherent load
+// (psi written by other blocks of the same launch, step_wave.cuh), ld_global_nc the read-only path.
+__device__ __forceinline__ double ld_global(const double *a) {
+  double v;
+  asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(a));
+  return v;
+}
+__device__ __forceinline__ double ld_global_nc(const double *a) {
+  double v;
+  asm("ld.global.nc.f64 %0, [%1];" : "=d"(v) : "l"(a));
+  return v;
+}
+__device__ __forceinline__ int ld_mask(const uint8_t *a) {
+  int v;
+  asm("ld.global.nc.u8 %0, [%1];" : "=r"(v) : "l"(a));
+  return v;
+}
+
 // L2 eviction-priority hints (createpolicy + ld/st .L2::cache_hint).  Used by the wave variant
 // (step_wave.cuh), whose psi items read populations that the fused items read again shortly
 // afterwards: first touch KEEP (evict_last), second touch and the freshly written populations
@@ -99,14 +142,14 @@ __device__ __forceinline__ uint64_t make_policy() {
 }
 template <int POL>
 __device__ __forceinline__ double load_pop(const double *a, uint64_t pol) {
-  if (POL == POL_DEFAULT) return __ldg(a);
+  if (POL == POL_DEFAULT) return ld_global_nc(a);
   double v;
   asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;\n" : "=d"(v) : "l"(a), "l"(pol));
   return v;
 }
 template <int POL>
 __device__ __forceinline__ void store_pop(double *a, double v, uint64_t pol) {
-  if (POL == POL_DEFAULT) { *a = v; return; }
+  if (POL == POL_DEFAULT) { asm volatile("st.global.f64 [%0], %1;" ::"l"(a), "d"(v) : "memory"); return; }
   asm volatile("st.global.L2::cache_hint.f64 [%0], %1, %2;\n" ::"l"(a), "d"(v), "l"(pol) : "memory");
 }
 
@@ -118,14 +161,28 @@ template <bool MASK, int POL = POL_DEFAULT>
 __device__ __forceinline__ void pull19(const double *__restrict__ ps, const uint8_t *__restrict__ ms, const Geom &g,
                                        const Nbr &n, double (&f)[Q]) {
   const uint64_t pol = make_policy<POL>();
+  if (POL == POL_DEFAULT) {
+    // stand-alone kernels: the compiler's own address arithmetic measured faster there
 #pragma unroll
-  for (int q = 0; q < Q; q++) {
-    const int d = n.ox[1 - cx(q)] + n.oy[1 - cy(q)];  // in-plane offset to the upstream site p - c_q
-    int src = q * g.plane - cz(q) * g.fz + d;
-    if (MASK && q > 0) {
-      if (ms[d - cz(q) * g.plane]) src = bounce(q) * g.plane;
+    for (int q = 0; q < Q; q++) {
+      const int d = n.ox[1 - cx(q)] + n.oy[1 - cy(q)];  // in-plane offset to the upstream site p - c_q
+      int src = q * g.plane - cz(q) * g.fz + d;
+      if (MASK && q > 0) {
+        if (ms[d - cz(q) * g.plane]) src = bounce(q) * g.plane;
+      }
+      f[q] = load_pop<POL>(ps + src, pol);
     }
-    f[q] = load_pop<POL>(ps + src, pol);
+  } else {
+    // wave variant: explicit 32-bit-offset addressing (ptr_at), -9 % instructions, +2 % throughput
+#pragma unroll
+    for (int q = 0; q < Q; q++) {
+      const int d = n.ox[1 - cx(q)] + n.oy[1 - cy(q)];
+      int src = q * g.plane - cz(q) * g.fz + d;
+      if (MASK && q > 0) {
+        if (ld_mask(ptr_at(ms, d - cz(q) * g.plane))) src = bounce(q) * g.plane;
+      }
+      f[q] = load_pop<POL>(ptr_at(ps, src), pol);
+    }
   }
 }
 

@@ -204,7 +204,7 @@ static cudaError_t wave_launch(const StepLaunch &L, int z_begin, int z_count) {
   w.xb = (g.nx + WAVE_SEG - 1) / WAVE_SEG;
   // lag of F behind P: at least 2 slots (F(z) reads psi(z+1)); more when a band-plane is smaller than
   // the ~80k sites the GPU keeps in flight, so that F blocks rarely have to wait
-  int la = e_la ? std::atoi(e_la) : (int)((65536 + (int64_t)w.tyb * g.nx - 1) / ((int64_t)w.tyb * g.nx));
+  int la = e_la ? std::atoi(e_la) : (int)((81920 + (int64_t)w.tyb * g.nx - 1) / ((int64_t)w.tyb * g.nx));
   if (la < 2) la = 2;
   if (!e_la && la > 8) la = 8;
   w.la = la;
@@ -232,7 +232,7 @@ static cudaError_t wave_launch(const StepLaunch &L, int z_begin, int z_count) {
   w.pf = e_pf ? std::atoi(e_pf) : 0;   // measured slower when on (profiles/r01_wave_experiments.md): L2 capacity, not latency, is the limit
   w.pf_keep = e_pfk ? std::atoi(e_pfk) : 1;
   static const char *e_batch = std::getenv("DLBC_WAVE_BATCH");
-  w.batch = e_batch ? std::atoi(e_batch) : 0;
+  w.batch = e_batch ? std::atoi(e_batch) : 1;  // with LA = 5: +2-4 % (LA = 4: -8 %), profiles/README.md
   wave_kernel<C, EQ, PSI, MASK, kExact, SPLIT><<<grid, dim3(WAVE_SEG, SPLIT ? C : 1), 0, L.stream>>>(g, L.f, L.p, w);
   return cudaGetLastError();
 }

@@ -71,13 +71,25 @@ template <int C, bool MASK, bool EXACT, bool COHERENT = false>
 __device__ __forceinline__ void shan_chen_force(const Geom &g, const Fields &fl, const StepParams &P, int zg,
                                                 const Nbr &n, const double (&psi1)[C], double (&F)[C][3]) {
   const uint8_t *ms = mask_plane(fl.mask, g, zg) + n.sxy;
-  const double *pp = psi_plane(fl.psi, g, zg, 0) + n.sxy;  // not __restrict__: see COHERENT
-  const int64_t cstride = g.sites_g;
-  sc_force<C, EXACT>(P, psi1, F, [&](int f2, int q) -> double {
-    const int d = n.ox[1 + cx(q)] + n.oy[1 + cy(q)] + cz(q) * g.plane;
-    if (MASK && ms[d]) return psi1[f2];
-    return COHERENT ? pp[f2 * cstride + d] : __ldg(pp + f2 * cstride + d);
-  });
+  if (!COHERENT) {
+    const double *pp = psi_plane(fl.psi, g, zg, 0) + n.sxy;
+    const int64_t cstride = g.sites_g;
+    sc_force<C, EXACT>(P, psi1, F, [&](int f2, int q) -> double {
+      const int d = n.ox[1 + cx(q)] + n.oy[1 + cy(q)] + cz(q) * g.plane;
+      if (MASK && ms[d]) return psi1[f2];
+      return __ldg(pp + f2 * cstride + d);
+    });
+  } else {
+    // psi was written by other blocks of this launch: coherent loads, 32-bit-offset addressing
+    const double *pp[C];
+#pragma unroll
+    for (int c = 0; c < C; c++) pp[c] = psi_plane(fl.psi, g, zg, c) + n.sxy;
+    sc_force<C, EXACT>(P, psi1, F, [&](int f2, int q) -> double {
+      const int d = n.ox[1 + cx(q)] + n.oy[1 + cy(q)] + cz(q) * g.plane;
+      if (MASK && ld_mask(ptr_at(ms, d))) return psi1[f2];
+      return ld_global(ptr_at(pp[f2], d));
+    });
+  }
 }
 
 // NOTE on ordering: the reference finishes ALL f2 for a given f1 (then the wall term of f1)
@@ -136,7 +148,10 @@ __device__ __forceinline__ void store19(const Geom &g, double *__restrict__ f_ne
   double *__restrict__ out = f_plane(f_new, g, zg, c) + sxy;
   const uint64_t pol = make_policy<POL>();
 #pragma unroll
-  for (int q = 0; q < Q; q++) store_pop<POL>(out + q * g.plane, f[q], pol);
+  for (int q = 0; q < Q; q++) {
+    if (POL == POL_DEFAULT) store_pop<POL>(out + q * g.plane, f[q], pol);
+    else store_pop<POL>(ptr_at(out, q * g.plane), f[q], pol);
+  }
   if (g.periodic_z_local) {
     if (zg == g.nz) {
       double *__restrict__ gh = f_plane(f_new, g, 0, c) + sxy;

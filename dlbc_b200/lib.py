@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(HERE, "libdlbc_cuda.so")
+SO_PATH = os.environ.get("DLBC_CUDA_LIB") or os.path.join(HERE, "libdlbc_cuda.so")  # override: A/B runs of two builds
 MAXC = 4
 NCCL_ID_BYTES = 128
 ABI_VERSION = 1
