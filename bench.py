@@ -194,6 +194,11 @@ def run_ours(args, rank, world, local_rank):
         sx, sy, sz = (int(v) for v in args.shape.split(","))
         gn = (sx, sy, sz * world)
     params = dict(cases.SC2) if ncomp == 2 else dict(tau=[1.0], eqdist_form="SecondOrder", enable_shan_chen=False)
+    porous = args.workload == "porous"
+    if porous:
+        if ncomp != 2:
+            raise SystemExit("--workload porous is the two-fluid BASELINE configs[3]")
+        params["global_acc"] = [0.0, 0.0, 1e-5]
     G = Lattice(gn, ncomp, **params, arithmetic=args.arith, kernel=args.kernel, device=local_rank,
                 rank=rank, nranks=world, nccl_id=nccl_id)
     gl = G.n
@@ -211,7 +216,24 @@ def run_ours(args, rank, world, local_rank):
         v, p = pinned_array(lib, (xc, gl[1], gl[2], 19))
         v[...] = cases.synthetic_layers(gl, xc, rho0, 0.01, form, 42 + 7 * rank + k)
         views.append(v); ptrs.append(p)
-    fill_lattice(G, gl, ncomp, views)
+    if porous:
+        # BASELINE configs[3]: random bounce-back geometry (30 % solid, synthetic PCG64 draw), fluids at
+        # rho = 0.7 / 0.04, solid sites initialised as initEqDistWall does (fields/init.d:469-477)
+        mask = (np.random.default_rng(1234 + rank).random(gl) < 0.3).astype(np.int32)
+        G.set_mask(mask)
+        wall = np.zeros(19); wall[0] = 1.0
+        eq = I.eq_dist_unity(cases.d3q19, form)
+        for c, rho in enumerate((0.7, 0.04)):
+            for x0 in range(0, gl[0], xc):
+                cnt = min(xc, gl[0] - x0)
+                blk = views[0][:cnt]
+                blk[...] = rho * eq
+                blk[mask[x0:x0 + cnt] != 0] = wall
+                G.set_populations_xrange(c, blk, x0)
+                G.sync()
+        args.no_e2e = True
+    else:
+        fill_lattice(G, gl, ncomp, views)
     G.sync()
 
     def barrier():
@@ -261,7 +283,7 @@ def run_ours(args, rank, world, local_rank):
             try:
                 with open(tp) as f:
                     tr = json.load(f).get(dom)
-                    if tr:  # ncu-measured DRAM bytes per site of this kernel x the sites of one launch
+                    if tr and not porous:  # ncu-measured DRAM bytes per site of this kernel x the sites of one launch
                         roof["traffic"] = tr["bytes_per_site"] * sites_local
                         roof["traffic_bytes_per_site"] = tr["bytes_per_site"]
                         roof["traffic_source"] = tr["source"]
@@ -309,7 +331,9 @@ def run_ours(args, rank, world, local_rank):
             "metric": METRIC, "value": value, "unit": "MLUPS", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": ("D3Q19 two-component Shan-Chen spinodal decomposition (BASELINE configs[2])"
+            "config": {"workload": ("D3Q19 two-fluid Shan-Chen flow through a random porous bounce-back geometry, "
+                                    "30 % solid (BASELINE configs[3])" if porous else
+                                    "D3Q19 two-component Shan-Chen spinodal decomposition (BASELINE configs[2])"
                                     if ncomp == 2 else "D3Q19 single-fluid BGK periodic (BASELINE configs[1])"),
                        "lattice": list(gn), "components": ncomp, "decomposition": f"{world} z-slab(s) of {list(gl)}",
                        "arithmetic": args.arith, "kernel": args.kernel,
@@ -332,6 +356,8 @@ def main():
     ap.add_argument("--size", type=int, default=512, help="lattice edge per GPU")
     ap.add_argument("--shape", default=None, help="nx,ny,nz per GPU (overrides --size; profiling runs)")
     ap.add_argument("--components", type=int, default=2)
+    ap.add_argument("--workload", default="spinodal", choices=["spinodal", "porous"],
+                    help="porous: BASELINE configs[3] (mask-heavy path), device-resident timing only")
     ap.add_argument("--arith", default="fast", choices=["fast", "exact"])
     ap.add_argument("--kernel", default="auto", choices=["auto", "two_pass", "zmarch", "zpipe", "wave"])
     ap.add_argument("--cpu-sample", type=int, default=128)

@@ -61,7 +61,10 @@ __device__ __forceinline__ void red_release_add(int *p, int v) {
   asm volatile("red.release.gpu.global.add.s32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
 }
 
-constexpr int WAVE_SEG = 128;  // sites per item == threads per block
+#ifndef DLBC_WAVE_SEG
+#define DLBC_WAVE_SEG 128
+#endif
+constexpr int WAVE_SEG = DLBC_WAVE_SEG;  // sites per item == threads per block (64 / 256 measured slower or equal)
 #ifndef WAVE_PREFETCH
 #define WAVE_PREFETCH true
 #endif
@@ -273,7 +276,7 @@ __device__ __forceinline__ void fused_site_split(const Geom &g, const Fields &fl
 
 // SPLIT: block = WAVE_SEG sites x C components (threadIdx.y = component), see above.
 template <int C, bool MASK, bool SPLIT>
-constexpr int wave_min_blocks() { return !SPLIT ? (MASK ? 3 : 4) : (C <= 2 ? 3 : (C == 3 ? 2 : 1)); }
+constexpr int wave_min_blocks() { return !SPLIT ? (MASK ? 3 : 4) * 128 / WAVE_SEG : (C <= 2 ? 3 : (C == 3 ? 2 : 1)); }
 
 template <int C, int EQ, int PSI, bool MASK, bool EXACT, bool SPLIT>
 __global__ void __launch_bounds__(WAVE_SEG * (SPLIT ? C : 1), (wave_min_blocks<C, MASK, SPLIT>()))

@@ -1,0 +1,236 @@
+"""Run one of the reference's 3-D parameter files through the GPU path -- SURVEY.md 8(f) row 1.
+
+    python -m dlbc_b200.replay case.in [--parameter name=value ...] [--out DIR] [--backend cuda|oracle]
+
+Plays the role of src/main.d for the lattice-Boltzmann subset: parse the parameter file
+(`dlbc_b200.params`), build mask and initial populations exactly as initMask / initFluids do for a
+one-rank run (lb/mask.d:134-172, lb/init.d:77-136; `dlbc_b200.init`), then step and collect the fields
+that dumpLBData would write (lb/io.d:56-101) at the frequencies the file asks for.  Outputs are keyed by
+the reference's file-name stem, ``<field>-<simulationName>-t%08d`` (io/io.d:157-172 without the
+time-stamp id), so they can be compared one to one with ``reference-data/*.h5``; ``--out`` writes them
+as ``.npy`` (the HDF5 writer is 8(f) row 2).
+
+Unsupported parameters fail loudly: electrokinetics, File inits, non-3-D lattices.  The `oracle`
+backend exists for the tests (CPU parity of the driver itself); the product backend is `cuda`.
+"""
+from __future__ import annotations
+
+import argparse
+import os
+
+import numpy as np
+
+from . import init as I
+from . import params as P
+from .connectivity import d3q19
+from .rng import Mt19937
+
+AXIS = {"X": 0, "Y": 1, "Z": 2}
+
+
+class ReplayError(ValueError):
+    pass
+
+
+def _fit(v, n, name, strict=False, fill=0):
+    """checkArrayParameterLength (parameters.d:262-283): empty -> zeros, wrong length -> fatal."""
+    v = list(v)
+    if not v and n:
+        if strict:
+            raise ReplayError(f"Array parameter {name} must have length {n}.")
+        return [fill] * n
+    if len(v) != n:
+        raise ReplayError(f"Array parameter {name} must have length {n}.")
+    return v
+
+
+def lattice_kwargs(p):
+    """Parameter dict -> (gn, components, kwargs of Lattice / OracleLattice)."""
+    gn = tuple(int(x) for x in p["lattice.gn"])
+    if len(gn) != 3:
+        raise ReplayError(f"lattice.gn = {list(gn)}: libdlbc_cuda implements D3Q19 only")
+    if p["elec.enableElec"]:
+        raise ReplayError("elec.enableElec = true: electrokinetics is outside the GPU path")
+    C = int(p["lb.components"])
+    sc = bool(p["lb.force.enableShanChen"])
+    kw = dict(tau=_fit(p["lb.tau"], C, "lb.lb.tau", strict=p["lb.timesteps"] > 0),
+              global_acc=_fit(p["lb.force.globalAcc"], 3, "lb.force.globalAcc", fill=0.0),
+              psi_form=p["lb.force.psiForm"], eqdist_form=p["lb.eqdist.eqDistForm"], enable_shan_chen=sc)
+    if sc:
+        gcc = _fit(p["lb.force.gcc"], C, "lb.force.gcc", strict=True)
+        kw["gcc"] = [_fit(row, C, f"lb.force.gcc[{i}]", strict=True) for i, row in enumerate(gcc)]
+        kw["gwc"] = _fit(p["lb.force.gwc"], C, "lb.force.gwc", fill=0.0)
+    return gn, C, kw
+
+
+def initial_mask(p, blk):
+    """initMask, lb/mask.d:134-172 (one rank)."""
+    kind = p["lb.mask.maskInit"]
+    axis = AXIS[p["lb.mask.initAxis"]]
+    if kind == "None":
+        return I.mask_none(blk)
+    if kind == "Box":
+        return I.mask_box(blk)
+    if kind == "Tube":
+        return I.mask_tube(blk, axis)
+    if kind == "Plates":
+        return I.mask_plates(blk, axis, p["lb.mask.wallOffset"])
+    if kind == "Walls":
+        dhw = _fit(p["lb.mask.dimensionHasWall"], 3, "lb.mask.dimensionHasWall", fill=[False, False])
+        return I.mask_walls(blk, [_fit(x, 2, "lb.mask.dimensionHasWall[i]", fill=False) for x in dhw],
+                            p["lb.mask.wallThickness"])
+    raise ReplayError(f"lb.mask.maskInit = {kind} is not supported by the replay driver")
+
+
+def initial_populations(p, blk, mask):
+    """initFluids, lb/init.d:77-136 (one rank: the rank shift of the seed is 0)."""
+    C = int(p["lb.components"])
+    form = I.EQDIST_FORMS[p["lb.eqdist.eqDistForm"]]
+    kinds = _fit(p["lb.init.fluidInit"], C, "lb.init.fluidInit", fill="None")
+    dens = _fit(p["lb.init.fluidDensities"], C, "lb.init.fluidDensities", fill=[])
+    perturb = _fit(p["lb.init.fluidPerturb"], C, "lb.init.fluidPerturb", fill=0.0)
+    reseed = _fit(p["lb.init.randomReseed"], C, "lb.init.randomReseed", fill=False)
+    seeds = _fit(p["lb.init.randomSeed"], C, "lb.init.randomSeed", fill=0)
+    off = _fit(p["lb.init.initOffset"], 3, "lb.init.initOffset", fill=0.0)
+    sep = _fit(p["lb.init.initSeparation"], 3, "lb.init.initSeparation", fill=0.0)
+    axis = AXIS[p["lb.init.initAxis"]]
+    radius, thick = p["lb.init.initRadius"], p["lb.init.interfaceThickness"]
+    widths = list(p["lb.init.lamellaeWidths"])
+    rng = Mt19937(p["random.seed"])  # the global generator (random.d:43-53), shared by the non-reseeding fluids
+    pops = []
+    for f in range(C):
+        lrng = Mt19937(seeds[f]) if reseed[f] else rng
+        k, d = kinds[f], list(dens[f])
+
+        def need(n):
+            if len(d) != n:
+                raise ReplayError(f"Array parameter lb.init.fluidDensities[{f}] must have length {n}.")
+        if k == "Const":
+            need(1); a = I.init_const(blk, 19, d[0])
+        elif k == "ConstRandom":
+            need(1); a = I.init_const_random(blk, 19, d[0], lrng)
+        elif k == "EqDist":
+            need(1); a = I.init_eq_dist(blk, d3q19, form, d[0])
+        elif k == "EqDistRandom":
+            need(1); a = I.init_eq_dist_random(blk, d3q19, form, d[0], lrng)
+        elif k == "EqDistPerturb":
+            need(1); a = I.init_eq_dist_perturb(blk, d3q19, form, d[0], perturb[f], lrng)
+        elif k == "EqDistPerturbFrac":
+            need(1); a = I.init_eq_dist_perturb_frac(blk, d3q19, form, d[0], perturb[f], lrng)
+        elif k == "EqDistSphere":
+            need(2); a = I.init_eq_dist_sphere(blk, d3q19, form, d[0], d[1], radius, off, thick)
+        elif k == "EqDistSphereFrac":
+            need(2); a = I.init_eq_dist_sphere_frac(blk, d3q19, form, d[0], d[1], radius, off, thick)
+        elif k == "EqDistTwoSpheres":
+            need(2); a = I.init_eq_dist_two_spheres(blk, d3q19, form, d[0], d[1], radius, off, thick, sep)
+        elif k == "EqDistTwoSpheresFrac":
+            need(2); a = I.init_eq_dist_two_spheres_frac(blk, d3q19, form, d[0], d[1], radius, off, thick, sep)
+        elif k == "EqDistCylinder":
+            need(2); a = I.init_eq_dist_cylinder(blk, d3q19, form, d[0], d[1], axis, radius, off, thick)
+        elif k == "EqDistCylinderFrac":
+            need(2); a = I.init_eq_dist_cylinder_frac(blk, d3q19, form, d[0], d[1], axis, radius, off, thick)
+        elif k == "EqDistLamellae":
+            need(len(widths)); a = I.init_eq_dist_lamellae(blk, d3q19, form, d, widths, axis, thick)
+        elif k == "EqDistLamellaeFrac":
+            need(len(widths)); a = I.init_eq_dist_lamellae_frac(blk, d3q19, form, d, widths, axis, thick)
+        else:
+            raise ReplayError(f"lb.init.fluidInit[{f}] = {k} is not supported by the replay driver")
+        pops.append(I.init_eq_dist_wall(np.ascontiguousarray(a), mask))  # lb/init.d:121
+    return pops
+
+
+def _dump_now(freq, t):
+    """io/io.d:224-226"""
+    return freq > 0 and t % freq == 0
+
+
+def _collect(L, p, t, out):
+    """dumpLBData, lb/io.d:56-101 (laplace output excluded)."""
+    if not p["io.enableIO"] or t < p["io.startOutput"]:  # io/io.d dumpData
+        return
+    names = list(p["lb.fieldNames"])
+    C = int(p["lb.components"])
+    sim = P.replace_fname_tokens(p["io.simulationName"], p)  # e.g. laplace-droplet-3d-gcc%lb.force.gcc[1][0]%
+
+    def put(stem, arr):
+        out[f"{stem}-{sim}-t{t:08d}"] = arr
+
+    io = lambda k: p[f"lb.io.{k}Freq"]
+    if _dump_now(io("population"), t):
+        for i in range(C):
+            put(f"population-{names[i]}", L.get_populations(i))
+    if _dump_now(io("density"), t):
+        for i in range(C):
+            put(f"density-{names[i]}", L.density(i))
+    if _dump_now(io("colour"), t):
+        for i in range(C):
+            for j in range(i + 1, C):
+                put(f"colour-{names[i]}-{names[j]}", L.colour(i, j))
+    if _dump_now(io("velocity"), t):
+        for i in range(C):
+            put(f"velocity-{names[i]}", L.velocity(i))
+    if _dump_now(io("force"), t):
+        for i in range(C):
+            put(f"force-{names[i]}", L.force(i))
+    if _dump_now(io("mask"), t):
+        put("mask", L.get_mask())
+
+
+def replay(p, backend="cuda", device=0, arithmetic="fast", kernel="auto"):
+    """Run the case described by parameter dict `p`; returns {file-name stem: array}."""
+    gn, C, kw = lattice_kwargs(p)
+    names = _fit(p["lb.fieldNames"], C, "lb.lb.fieldNames", strict=True)
+    p = dict(p, **{"lb.fieldNames": names})
+    blk = I.Block(gn)
+    mask = initial_mask(p, blk)
+    pops = initial_populations(p, blk, mask)
+    if backend == "cuda":
+        from .lattice import Lattice
+        L = Lattice(gn, C, **kw, device=device, arithmetic=arithmetic, kernel=kernel)
+    elif backend == "oracle":  # tests only
+        from oracle import oracle as O
+        L = O.OracleLattice(gn, C, **kw)
+    else:
+        raise ReplayError(f"unknown backend {backend!r}")
+    out = {}
+    try:
+        L.set_mask(mask, halo=blk.halo)
+        for c, a in enumerate(pops):
+            L.set_populations(c, a, halo=blk.halo)
+        if backend == "oracle":
+            L.exchange_halo()  # main.d:142
+        _collect(L, p, 0, out)  # "First data dump", main.d:149
+        freqs = [p[f"lb.io.{k}Freq"] for k in ("population", "density", "colour", "velocity", "force", "mask")]
+        freqs = sorted({f for f in freqs if f > 0})
+        t, T = 0, int(p["lb.timesteps"])
+        while t < T:
+            nxt = min([T] + [(t // f + 1) * f for f in freqs])  # next step at which anything is dumped
+            L.step(nxt - t)
+            t = nxt
+            _collect(L, p, t, out)
+    finally:
+        if backend == "cuda":
+            L.close()
+    return out
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser(description=__doc__.split("\n\n")[0])
+    ap.add_argument("parameter_file")
+    ap.add_argument("-p", "--parameter", action="append", default=[], metavar="name=value",
+                    help="override, as the reference's --parameter (repeatable)")
+    ap.add_argument("--out", default=None, help="directory for <stem>.npy files")
+    ap.add_argument("--backend", default="cuda", choices=["cuda", "oracle"])
+    ap.add_argument("--arith", default="fast", choices=["fast", "exact"])
+    a = ap.parse_args(argv)
+    p = P.parse_file(a.parameter_file, a.parameter)
+    out = replay(p, backend=a.backend, arithmetic=a.arith)
+    for k, v in out.items():
+        print(f"{k}: shape {v.shape}, sum {float(np.sum(v)):.15g}")
+        if a.out:
+            os.makedirs(a.out, exist_ok=True)
+            np.save(os.path.join(a.out, k + ".npy"), v)
+
+
+if __name__ == "__main__":
+    main()

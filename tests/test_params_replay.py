@@ -1,0 +1,149 @@
+"""Parameter-file reader + replay driver.
+
+The ``.in`` files under tests/golden/in/ are the reference's own test inputs
+(tests/runnable/tests/lb/<case>/<case>.in), replayed unmodified; overrides are the ones the reference's
+test JSON applies in its "fast" variants (dlbct/test.py).  CPU tests drive the oracle backend (they test the
+reader and the driver); the GPU tests drive libdlbc_cuda through the same code path.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from dlbc_b200 import params as P
+from dlbc_b200 import replay as R
+from helpers import assert_bitexact, assert_close
+
+IN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "in")
+
+
+# ---- reader ---------------------------------------------------------------------------------------
+def test_reader_sections_comments_literals():
+    text = """
+    // leading comment
+    [lb]
+    timesteps = 10   // trailing comment
+    tau = [ 1.0, 0.8 ]
+    fieldNames = [ "red", blue ]
+    eqdist.eqDistForm = BDist2
+    force.gcc = [ [ 0.0, 3.6 ], [ 3.6, 0.0 ] ]
+    init.randomReseed = [ True, false ]
+    [lattice]
+    gn = [64, 32, 16 ]
+    [io]
+    simulationName = my-sim
+    """
+    p = P.parse_text(text)
+    assert p["lb.timesteps"] == 10 and p["lb.tau"] == [1.0, 0.8]
+    assert p["lb.fieldNames"] == ["red", "blue"]
+    assert p["lb.eqdist.eqDistForm"] == "BDist2"
+    assert p["lb.force.gcc"] == [[0.0, 3.6], [3.6, 0.0]]
+    assert p["lb.init.randomReseed"] == [True, False]
+    assert p["lattice.gn"] == [64, 32, 16] and p["io.simulationName"] == "my-sim"
+    assert p["lb.components"] == 1 and p["random.shiftSeedByRank"] is True  # defaults of the reference
+    assert "lb.tau" in p["_set"] and "lb.components" not in p["_set"]
+
+
+def test_reader_unknown_key_is_fatal_and_names_the_line():
+    with pytest.raises(P.ParameterError, match=r"Unknown key at line 3: 'lb.tua'"):
+        P.parse_text("[lb]\ntimesteps = 1\ntua = [ 1.0 ]\n")
+    with pytest.raises(P.ParameterError, match=r"Unknown key from command line: 'lb.nope'"):
+        P.parse_text("[lb]\ntimesteps = 1\n", ["lb.nope=3"])
+    with pytest.raises(P.ParameterError, match="not a member of EqDistForm"):
+        P.parse_text("[lb]\neqdist.eqDistForm = FourthOrder\n")
+    with pytest.raises(P.ParameterError, match="unbalanced"):
+        P.parse_text("[lb]\ntau = [ 1.0, 2.0\n")
+
+
+def test_reader_overrides_apply_after_the_file():
+    p = P.parse_file(os.path.join(IN, "merging-droplets-3d.in"), ["lb.timesteps=10", "lb.io.densityFreq = 10"])
+    assert p["lb.timesteps"] == 10 and p["lb.io.densityFreq"] == 10 and p["lb.io.colourFreq"] == 1000
+    assert p["lb.init.fluidInit"] == ["EqDistTwoSpheresFrac"] * 2 and p["lb.init.initSeparation"] == [0.4, 0.0, 0.0]
+
+
+@pytest.mark.parametrize("name", sorted(os.listdir(IN)))
+def test_reader_accepts_every_fixture(name):
+    p = P.parse_file(os.path.join(IN, name))
+    gn, C, kw = R.lattice_kwargs(p)
+    assert len(gn) == 3 and C == 2 and len(kw["tau"]) == 2
+
+
+def test_fname_tokens():
+    p = P.parse_file(os.path.join(IN, "laplace-droplet-3d.in"))
+    assert P.replace_fname_tokens(p["io.simulationName"], p) == "laplace-droplet-3d-gcc3.6"
+    assert P.replace_fname_tokens("x-%lb.components%-%lb.tau[1]%-%lb.force.enableShanChen%", p) == "x-2-1-true"
+    with pytest.raises(P.ParameterError):
+        P.replace_fname_tokens("%lb.tau[7]%", p)
+
+
+def test_driver_rejects_what_the_gpu_path_does_not_cover():
+    base = "[lattice]\ngn = [8, 8, 8]\n[lb]\ncomponents = 1\ntau = [1.0]\ntimesteps = 1\n"
+    with pytest.raises(R.ReplayError, match="D3Q19"):
+        R.lattice_kwargs(P.parse_text(base.replace("[8, 8, 8]", "[8, 8]")))
+    with pytest.raises(R.ReplayError, match="electrokinetics"):
+        R.lattice_kwargs(P.parse_text(base + "[elec]\nenableElec = true\n"))
+    with pytest.raises(R.ReplayError, match="lb.lb.tau"):
+        R.lattice_kwargs(P.parse_text(base.replace("tau = [1.0]\n", "")))
+
+
+# ---- replay: CPU (oracle backend) -------------------------------------------------------------------
+FAST = {  # the "fast" parameter sets of the reference's test JSON files
+    "merging-droplets-3d": ["lb.timesteps=10", "lb.io.colourFreq=10", "lb.io.densityFreq=10"],
+    "laplace-droplet-3d": ["lb.timesteps=10", "lb.io.colourFreq=10", "lb.io.densityFreq=10", "lb.io.laplaceFreq=0"],
+    "bdist2-sc-3d": ["lb.timesteps=10", "lb.io.colourFreq=10", "lb.io.densityFreq=10", "lb.io.populationFreq=10"],
+    "bdist2-3d": [],
+}
+
+
+SIM = {"laplace-droplet-3d": "laplace-droplet-3d-gcc3.6"}  # simulationName with its %lb.force.gcc[1][0]% token replaced
+
+
+def _check(case, out, g, tol, times):
+    """Compare every golden array of `case` at `times` with the replayed output of the same name."""
+    n = 0
+    for key, ref in g.items():
+        stem, t = key.rsplit("-t", 1)
+        if int(t) not in times:
+            continue
+        got = out[f"{stem}-{SIM.get(case, case)}-t{int(t):08d}"]
+        if ref.shape != got.shape:  # bdist2-sc-3d goldens hold the line along z (the run is uniform in x, y)
+            assert np.array_equal(got, np.broadcast_to(got[0:1, 0:1], got.shape)), key
+            got = got[0, 0]
+        if tol == 0:
+            assert_bitexact(got, ref, key)
+        elif tol == "rel":
+            assert_close(got, ref, what=key)
+        else:
+            assert float(np.max(np.abs(got - ref))) <= tol, key
+        n += 1
+    assert n > 0
+    return n
+
+
+@pytest.mark.parametrize("case,times,tol", [("merging-droplets-3d", (0, 10), 1e-15), ("bdist2-3d", (0, 10), 0),
+                                            ("bdist2-sc-3d", (0, 10), 1e-15), ("laplace-droplet-3d", (0, 10), 1e-15)])
+def test_replay_reference_case_on_the_oracle(golden, case, times, tol):
+    p = P.parse_file(os.path.join(IN, case + ".in"), FAST[case])
+    out = R.replay(p, backend="oracle")
+    g = golden(case)
+    _check(case, {k: v for k, v in out.items() if k.endswith("t00000000")}, {k: v for k, v in g.items() if k.endswith("-t0")}, 0, (0,))
+    _check(case, out, g, tol, times)
+
+
+# ---- replay: GPU ------------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("case,times", [("merging-droplets-3d", (0, 10)), ("bdist2-3d", (0, 10)),
+                                        ("bdist2-sc-3d", (0, 10)), ("laplace-droplet-3d", (0, 10))])
+def test_replay_reference_case_on_the_gpu(golden, case, times):
+    p = P.parse_file(os.path.join(IN, case + ".in"), FAST[case])
+    out = R.replay(p, backend="cuda")
+    _check(case, out, golden(case), "rel", times)
+
+
+@pytest.mark.gpu
+def test_replay_full_length_cases_on_the_gpu(golden):
+    """bdist2-sc-3d unmodified (100 steps, populations) and laplace-droplet-3d to t = 100."""
+    p = P.parse_file(os.path.join(IN, "bdist2-sc-3d.in"))
+    _check("bdist2-sc-3d", R.replay(p, backend="cuda"), golden("bdist2-sc-3d"), "rel", (0, 100))
+    p = P.parse_file(os.path.join(IN, "laplace-droplet-3d.in"), ["lb.timesteps=100", "lb.io.laplaceFreq=0"])
+    _check("laplace-droplet-3d", R.replay(p, backend="cuda"), golden("laplace-droplet-3d"), "rel", (0, 100))
