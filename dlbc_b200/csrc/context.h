@@ -25,6 +25,7 @@ struct dlbc_cuda_ctx {
   double *psi = nullptr;              // [C][sites_g]
   double *rho_wall = nullptr;         // [C][sites_g], lazily built when gwc != 0 and solids exist
   uint8_t *mask = nullptr;            // [sites_g]
+  uint32_t *nbmask = nullptr;         // [sites_g] neighbourhood solid flags (Fields::nb), allocated when solids exist
   bool has_solid = false;
   bool rho_wall_valid = false;
   bool ghosts_valid = false;          // f[cur] ghost planes hold the neighbours' boundary planes

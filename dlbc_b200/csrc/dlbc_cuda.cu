@@ -112,6 +112,7 @@ StepLaunch make_launch(dlbc_cuda_ctx *ctx, cudaStream_t s) {
   L.f.psi = ctx->psi;
   L.f.rho_wall = ctx->rho_wall;
   L.f.mask = ctx->mask;
+  L.f.nb = ctx->nbmask;
   L.p = ctx->p;
   L.eq = ctx->cfg.eqdist_form;
   L.psi = ctx->cfg.psi_form;
@@ -445,6 +446,7 @@ int dlbc_cuda_destroy(dlbc_cuda_ctx *ctx) {
   if (ctx->nccl) nccl_api().CommDestroy(ctx->nccl);
   for (double *p : {ctx->f[0], ctx->f[1], ctx->psi, ctx->rho_wall, ctx->partial}) if (p) cudaFree(p);
   if (ctx->mask) cudaFree(ctx->mask);
+  if (ctx->nbmask) cudaFree(ctx->nbmask);
   if (ctx->stage) cudaFree(ctx->stage);
   if (ctx->flags) cudaFree(ctx->flags);
   for (int *p : ctx->wave_sync) if (p) cudaFree(p);
@@ -690,6 +692,15 @@ int dlbc_cuda_upload_mask(dlbc_cuda_ctx *ctx, const int32_t *mask, int halo) {
   }
   CK(cudaStreamSynchronize(ctx->compute));
   ctx->has_solid = solid > 0;
+  if (ctx->has_solid) {
+    if (!ctx->nbmask) {
+      const size_t bytes = (size_t)g.sites_g * sizeof(uint32_t);
+      CK(cudaMalloc(&ctx->nbmask, bytes));
+      ctx->device_bytes += (int64_t)bytes;
+    }
+    CK(launch_neighbour_bits(g, ctx->mask, ctx->nbmask, ctx->compute));
+    ctx->launches++;
+  }
   ctx->rho_wall_valid = false;
   ctx->force_valid = false;
   return release_stage(ctx);

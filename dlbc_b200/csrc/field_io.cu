@@ -133,6 +133,29 @@ __global__ void ghost_fill_mask_kernel(Geom g, uint8_t *__restrict__ m) {
   m[i] = m[(int64_t)g.nz * g.plane + i];
   m[(int64_t)(g.nz + 1) * g.plane + i] = m[g.plane + i];
 }
+// Fields::nb: bit q of nb[site] = mask[site + c_q] is Solid (bit 0 = the site itself), for the physical
+// planes 1..nz; x and y wrap periodically, z neighbours come from the (already valid) ghost planes.
+// Built once per mask upload: the geometry is static (the reference re-reads and re-exchanges the mask
+// every step, lattice.d:200-214).
+__global__ void neighbour_bits_kernel(Geom g, const uint8_t *__restrict__ m, uint32_t *__restrict__ nb) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= g.nx) return;
+  const int y = blockIdx.y, zg = 1 + blockIdx.z;
+  const Nbr n = make_nbr(g, x, y);
+  const uint8_t *ms = m + (int64_t)zg * g.plane + n.sxy;
+  uint32_t bits = 0;
+#pragma unroll
+  for (int q = 0; q < Q; q++) {
+    if (ms[n.ox[1 + cx(q)] + n.oy[1 + cy(q)] + cz(q) * g.plane]) bits |= 1u << q;
+  }
+  nb[(int64_t)zg * g.plane + n.sxy] = bits;
+}
+cudaError_t launch_neighbour_bits(const Geom &g, const uint8_t *m, uint32_t *nb, cudaStream_t s) {
+  const unsigned bx = g.nx >= 128 ? 128 : ((g.nx + 31) / 32) * 32;
+  neighbour_bits_kernel<<<dim3((g.nx + bx - 1) / bx, g.ny, g.nz), bx, 0, s>>>(g, m, nb);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_ghost_fill(const Geom &g, double *f, int narrays, cudaStream_t s) {
   dim3 grid((unsigned)((g.plane + 255) / 256), (unsigned)min(narrays, 65535));
   ghost_fill_kernel<<<grid, 256, 0, s>>>(g, f, narrays);

@@ -23,6 +23,8 @@ cudaError_t launch_mask_out(const Geom &g, const uint8_t *in, int32_t *out, cuda
 // ghost planes when the slab is its own z neighbour (nranks == 1), fields [narrays][zg][y][x]
 cudaError_t launch_ghost_fill(const Geom &g, double *f, int narrays, cudaStream_t s);
 cudaError_t launch_ghost_fill_mask(const Geom &g, uint8_t *m, cudaStream_t s);
+// neighbourhood solid flags (Fields::nb) of the physical planes from a mask whose ghost planes are valid
+cudaError_t launch_neighbour_bits(const Geom &g, const uint8_t *m, uint32_t *nb, cudaStream_t s);
 
 // derived outputs into a dense, halo-free device array [nx][ny][nz][K]
 // kind 0 density(c1), 1 colour(c1 - c2), 2 raw velocity(c1), 3 copy of an SoA vector field [3][sites_g]

@@ -34,6 +34,7 @@ struct Fields {
   double *psi;           // [C][sites_g]
   const double *rho_wall;// [C][sites_g] static own-site densities (only when gwc != 0 and solids exist)
   const uint8_t *mask;   // [sites_g]
+  const uint32_t *nb;    // [sites_g] bit q: site p + c_q is Solid (bit 0: p itself); only when solids exist
 };
 
 __host__ __device__ __forceinline__ int64_t f_index(const Geom &g, int c, int q, int zg, int64_t sxy) {
@@ -183,6 +184,24 @@ __device__ __forceinline__ void pull19(const double *__restrict__ ps, const uint
       }
       f[q] = load_pop<POL>(ptr_at(ps, src), pol);
     }
+  }
+}
+
+// The same with the neighbourhood's solid flags in a register (Fields::nb: bit q = site p + c_q is Solid)
+// instead of 18 byte loads per component whose results steer the addresses of the population loads:
+// one 4-byte load per site serves every component, the streaming step and the force (geometry is static,
+// the bits are built once at mask upload).  bounce-back of direction q looks at p - c_q, i.e. bit bounce(q).
+template <int POL = POL_DEFAULT>
+__device__ __forceinline__ void pull19_bits(const double *__restrict__ ps, uint32_t bits, const Geom &g, const Nbr &n,
+                                            double (&f)[Q]) {
+  const uint64_t pol = make_policy<POL>();
+#pragma unroll
+  for (int q = 0; q < Q; q++) {
+    const int d = n.ox[1 - cx(q)] + n.oy[1 - cy(q)];
+    int src = q * g.plane - cz(q) * g.fz + d;
+    if (q > 0 && ((bits >> bounce(q)) & 1u)) src = bounce(q) * g.plane;
+    if (POL == POL_DEFAULT) f[q] = load_pop<POL>(ps + src, pol);
+    else f[q] = load_pop<POL>(ptr_at(ps, src), pol);
   }
 }
 

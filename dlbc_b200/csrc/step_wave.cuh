@@ -276,7 +276,7 @@ __device__ __forceinline__ void fused_site_split(const Geom &g, const Fields &fl
 
 // SPLIT: block = WAVE_SEG sites x C components (threadIdx.y = component), see above.
 template <int C, bool MASK, bool SPLIT>
-constexpr int wave_min_blocks() { return !SPLIT ? (MASK ? 3 : 4) * 128 / WAVE_SEG : (C <= 2 ? 3 : (C == 3 ? 2 : 1)); }
+constexpr int wave_min_blocks() { return !SPLIT ? (MASK ? DLBC_MASK_BLOCKS : 4) * 128 / WAVE_SEG : (C <= 2 ? 3 : (C == 3 ? 2 : 1)); }
 
 template <int C, int EQ, int PSI, bool MASK, bool EXACT, bool SPLIT>
 __global__ void __launch_bounds__(WAVE_SEG * (SPLIT ? C : 1), (wave_min_blocks<C, MASK, SPLIT>()))

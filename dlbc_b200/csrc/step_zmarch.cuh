@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(TX *TY, MINB) zmarch_kernel(Geom g, Fields fl,
       if (MASK) { if (mp[n.at(cx(q), cy(q)) + cz(q) * g.plane]) return psi1[f2]; }
       return ring[(((zg + cz(q)) & 3) * C + f2) * RP + cell + cy(q) * RW + cx(q)];
     });
-    if (MASK && P.any_gwc) wall_force<C>(g, fl, P, zg, n, psi1, F);
+    if (MASK && P.any_gwc) wall_force<C>(g, fl, P, zg, n, 0u, psi1, F);
     double u[3] = {0.0, 0.0, 0.0};
     if (EQ == 2) common_velocity<C, EXACT>(P, m, rho, u);
 #pragma unroll
