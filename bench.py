@@ -189,10 +189,11 @@ def run_ours(args, rank, world, local_rank):
 
     n = args.size
     ncomp = args.components
-    gn = (n, n, n * world)
+    strong = args.scaling == "strong"
+    gn = (n, n, n if strong else n * world)   # weak: `size`^3 per GPU stacked in z; strong: `size`^3 in total
     if args.shape:
         sx, sy, sz = (int(v) for v in args.shape.split(","))
-        gn = (sx, sy, sz * world)
+        gn = (sx, sy, sz if strong else sz * world)
     params = dict(cases.SC2) if ncomp == 2 else dict(tau=[1.0], eqdist_form="SecondOrder", enable_shan_chen=False)
     porous = args.workload == "porous"
     if porous:
@@ -329,7 +330,7 @@ def run_ours(args, rank, world, local_rank):
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": "MLUPS", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": ("D3Q19 two-fluid Shan-Chen flow through a random porous bounce-back geometry, "
                                     "30 % solid (BASELINE configs[3])" if porous else
@@ -356,6 +357,8 @@ def main():
     ap.add_argument("--size", type=int, default=512, help="lattice edge per GPU")
     ap.add_argument("--shape", default=None, help="nx,ny,nz per GPU (overrides --size; profiling runs)")
     ap.add_argument("--components", type=int, default=2)
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak (default): --size^3 per GPU; strong: --size^3 in total, split into z-slabs")
     ap.add_argument("--workload", default="spinodal", choices=["spinodal", "porous"],
                     help="porous: BASELINE configs[3] (mask-heavy path), device-resident timing only")
     ap.add_argument("--arith", default="fast", choices=["fast", "exact"])
