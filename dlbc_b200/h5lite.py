@@ -220,3 +220,89 @@ def read_dataset(path, name="OutArray"):
 
 def list_root(path):
     return sorted(_File(path).links())
+
+
+# ---- writer ---------------------------------------------------------------------------------------
+# The profile the reference writes with writeChunked = false (src/dlbc/io/hdf5.d:125-285): one contiguous
+# dataset /OutArray in an old-style root group.  Superblock v0, object headers v1, dataspace v1, data layout
+# v3 -- the same on-disk structures the reference's own files use (read back by this module's reader and
+# laid out like the libhdf5-written golden files; there is no libhdf5 in this image to cross-check with).
+# Not written: the "input"/"metadata"/"globals" attribute groups of hdf5.d:453-548 (h5diff on /OutArray,
+# which is what the reference's test harness runs, does not look at them).
+
+def _pad8(b):
+    return b + b"\0" * (-len(b) % 8)
+
+
+def _msg(typ, body):
+    body = _pad8(body)
+    return struct.pack("<HHB3x", typ, len(body), 0) + body
+
+
+def _ohdr(msgs):
+    data = b"".join(msgs)
+    return struct.pack("<BxHII4x", 1, len(msgs), 1, len(data)) + data
+
+
+def _datatype(dtype):
+    dtype = np.dtype(dtype)
+    if dtype == np.dtype("<f8"):  # IEEE binary64, little-endian, implied mantissa msb, sign bit 63
+        return struct.pack("<B3BI", 0x11, 0x20, 0x3F, 0x00, 8) + struct.pack("<HHBBBBI", 0, 64, 52, 11, 0, 52, 1023)
+    if dtype == np.dtype("<i4"):  # two's complement, little-endian (H5T_NATIVE_INT, hdf5.d:90-92)
+        return struct.pack("<B3BI", 0x10, 0x08, 0x00, 0x00, 4) + struct.pack("<HH", 0, 32)
+    raise H5Error(f"dtype {dtype} unsupported (need <f8 or <i4)")
+
+
+def write_dataset(path, array, name="OutArray"):
+    """Write `array` (float64 or int32, C order) as the contiguous dataset /<name> of a new HDF5 file."""
+    a = np.ascontiguousarray(array)
+    if a.dtype == np.float64:
+        a = a.astype("<f8", copy=False)
+    elif a.dtype == np.int32:
+        a = a.astype("<i4", copy=False)
+    else:
+        raise H5Error(f"dtype {a.dtype} unsupported (need float64 or int32)")
+    K_LEAF, K_INT = 4, 16
+    nm = name.encode() + b"\0"
+    heap_data = _pad8(b"\0") + _pad8(nm)                       # offset 0: "", offset 8: name
+    name_off = 8
+    o_root = 96
+    root = _ohdr([_msg(0x11, struct.pack("<QQ", 0, 0))])        # patched below
+    o_btree = o_root + len(root)
+    btree_size = 24 + (2 * K_INT + 1) * 8 + 2 * K_INT * 8
+    o_heap = o_btree + btree_size
+    o_heap_data = o_heap + 32
+    o_snod = o_heap_data + len(heap_data)
+    snod_size = 8 + 2 * K_LEAF * 40
+    o_dset = o_snod + snod_size
+    rank = a.ndim
+    dataspace = struct.pack("<BBBx4x", 1, rank, 0) + struct.pack(f"<{rank}Q", *a.shape)
+    fill = bytes([2, 2, 2, 1, 0, 0, 0, 0])                      # v2: late allocation, fill if set, default value
+    layout_len = len(_msg(0x08, struct.pack("<BBQQ", 3, 1, 0, 0)))
+    dset_len = 16 + len(_msg(0x01, dataspace)) + len(_msg(0x03, _datatype(a.dtype))) + len(_msg(0x05, fill)) + layout_len
+    o_data = (o_dset + dset_len + 7) // 8 * 8
+    eof = o_data + a.nbytes
+    dset = _ohdr([_msg(0x01, dataspace), _msg(0x03, _datatype(a.dtype)), _msg(0x05, fill),
+                  _msg(0x08, struct.pack("<BBQQ", 3, 1, o_data, a.nbytes))])
+    assert len(dset) == dset_len
+    root = _ohdr([_msg(0x11, struct.pack("<QQ", o_btree, o_heap))])
+    sb = _SIG + bytes([0, 0, 0, 0, 0, 8, 8, 0]) + struct.pack("<HHI", K_LEAF, K_INT, 0)
+    sb += struct.pack("<QQQQ", 0, _UNDEF, eof, _UNDEF)
+    sb += struct.pack("<QQI4xQQ", 0, o_root, 1, o_btree, o_heap)  # root group symbol table entry
+    assert len(sb) == 96
+    btree = b"TREE" + struct.pack("<BBHQQ", 0, 0, 1, _UNDEF, _UNDEF) + struct.pack("<QQQ", 0, o_snod, name_off)
+    btree += b"\0" * (btree_size - len(btree))
+    heap = b"HEAP" + struct.pack("<B3xQQQ", 0, len(heap_data), 1, o_heap_data)  # free-list head 1 = none
+    snod = b"SNOD" + struct.pack("<BxH", 1, 1) + struct.pack("<QQI4x16x", name_off, o_dset, 0)
+    snod += b"\0" * (snod_size - len(snod))
+    with open(path, "wb") as fh:
+        fh.write(sb + root + btree + heap + heap_data + snod + dset)
+        fh.write(b"\0" * (o_data - (o_dset + dset_len)))
+        fh.write(a.tobytes())
+    return path
+
+
+def field_file_name(field, simulation_name, timestep, time_id="00000000T000000"):
+    """makeFilenameOutput (io/io.d:157-172): <field>-<simulationName>-<id>-t%08d.h5; the reference's id is
+    the start time of the run (yyyymmddThhmmss)."""
+    return f"{field}-{simulation_name}-{time_id}-t{int(timestep):08d}.h5"

@@ -8,7 +8,7 @@ one-rank run (lb/mask.d:134-172, lb/init.d:77-136; `dlbc_b200.init`), then step 
 that dumpLBData would write (lb/io.d:56-101) at the frequencies the file asks for.  Outputs are keyed by
 the reference's file-name stem, ``<field>-<simulationName>-t%08d`` (io/io.d:157-172 without the
 time-stamp id), so they can be compared one to one with ``reference-data/*.h5``; ``--out`` writes them
-as ``.npy`` (the HDF5 writer is 8(f) row 2).
+as HDF5 files with one contiguous ``/OutArray`` dataset each (`dlbc_b200.h5lite.write_dataset`, 8(f) row 2).
 
 Unsupported parameters fail loudly: electrokinetics, File inits, non-3-D lattices.  The `oracle`
 backend exists for the tests (CPU parity of the driver itself); the product backend is `cuda`.
@@ -219,17 +219,21 @@ def main(argv=None):
     ap.add_argument("parameter_file")
     ap.add_argument("-p", "--parameter", action="append", default=[], metavar="name=value",
                     help="override, as the reference's --parameter (repeatable)")
-    ap.add_argument("--out", default=None, help="directory for <stem>.npy files")
+    ap.add_argument("--out", default=None, help="directory for the HDF5 files (/OutArray, the reference's names)")
+    ap.add_argument("--run-id", default="00000000T000000", help="time-stamp id in the file names (io/io.d:157-172)")
     ap.add_argument("--backend", default="cuda", choices=["cuda", "oracle"])
     ap.add_argument("--arith", default="fast", choices=["fast", "exact"])
     a = ap.parse_args(argv)
     p = P.parse_file(a.parameter_file, a.parameter)
     out = replay(p, backend=a.backend, arithmetic=a.arith)
+    from . import h5lite
     for k, v in out.items():
         print(f"{k}: shape {v.shape}, sum {float(np.sum(v)):.15g}")
         if a.out:
+            # the reference's file name (io/io.d:157-172): <field>-<sim>-<run id>-t%08d.h5, dataset /OutArray
             os.makedirs(a.out, exist_ok=True)
-            np.save(os.path.join(a.out, k + ".npy"), v)
+            stem, t = k.rsplit("-t", 1)
+            h5lite.write_dataset(os.path.join(a.out, f"{stem}-{a.run_id}-t{t}.h5"), v)
 
 
 if __name__ == "__main__":
