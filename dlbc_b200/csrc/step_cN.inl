@@ -233,6 +233,11 @@ static cudaError_t wave_launch(const StepLaunch &L, int z_begin, int z_count) {
   w.pf_keep = e_pfk ? std::atoi(e_pfk) : 1;
   static const char *e_batch = std::getenv("DLBC_WAVE_BATCH");
   w.batch = e_batch ? std::atoi(e_batch) : 1;  // with LA = 5: +2-4 % (LA = 4: -8 %), profiles/README.md
+  static const char *e_free = std::getenv("DLBC_WAVE_FREE");  // 1: barrier-free form (wave_free_kernel)
+  if (!SPLIT && (e_free ? std::atoi(e_free) != 0 : false)) {
+    wave_free_kernel<C, EQ, PSI, MASK, kExact><<<grid, WAVE_SEG, 0, L.stream>>>(g, L.f, L.p, w);
+    return cudaGetLastError();
+  }
   wave_kernel<C, EQ, PSI, MASK, kExact, SPLIT><<<grid, dim3(WAVE_SEG, SPLIT ? C : 1), 0, L.stream>>>(g, L.f, L.p, w);
   return cudaGetLastError();
 }

@@ -351,4 +351,106 @@ wave_kernel(Geom g, Fields fl, StepParams P, Wave w) {
   }
 }
 
+
+// ---- barrier-free form ---------------------------------------------------------------------------
+// Same items, same ticket order, same per-site functions as wave_kernel, but the four warps of a block
+// never meet at a block barrier: in wave_kernel 20 % of the warp time was barrier stall (every warp
+// waiting for the block's slowest at the psi-plane poll, at the P completion and at the ticket hand-over;
+// profiles/README.md).  Here
+//   * the ticket of the block's next item is fetched by warp 0 and handed over through a small ring in
+//     shared memory; a warp that finishes early only waits for warp 0 to have published, and warp 0
+//     only waits if it is RING items ahead of the slowest warp (s_prog), so slots are never overwritten
+//     before every warp has read them;
+//   * P completion is counted per warp (target: rp * warps per block), each warp releasing after its own
+//     __syncwarp; F items poll the three psi planes per warp.
+// Deadlock freedom is unchanged: a warp only ever waits for items with smaller tickets or for its own
+// block's warp 0, which waits for nobody unless it is RING items ahead.
+constexpr int WAVE_RING = 4;
+
+template <int C, int EQ, int PSI, bool MASK, bool EXACT>
+__global__ void __launch_bounds__(WAVE_SEG, (wave_min_blocks<C, MASK, false>()))
+wave_free_kernel(Geom g, Fields fl, StepParams P, Wave w) {
+  constexpr int NW = WAVE_SEG / 32;
+  __shared__ int s_ring[WAVE_RING];
+  __shared__ int s_prog[NW];  // index of the last item whose ticket warp i has read
+  volatile int *ring = s_ring;
+  volatile int *prog = s_prog;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int per_slot = w.rp + w.rf;
+  const int per_band = w.slots * per_slot;
+  const int total = w.nbands * per_band;
+  const int p_target = w.rp * NW;
+  if (threadIdx.x == 0) ring[0] = atomicAdd(w.sync, 1);
+  else if (threadIdx.x < WAVE_RING) ring[threadIdx.x] = -1;
+  if (threadIdx.x < NW) prog[threadIdx.x] = 0;
+  __syncthreads();  // the only block barrier
+  int t = ring[0];
+  for (int n = 0; t < total; n++) {
+    int nxt = 0;
+    if (threadIdx.x == 0) nxt = atomicAdd(w.sync, 1);  // ticket of item n + 1, in flight during this item's work
+
+    const int band = t / per_band;
+    const int r = t - band * per_band;
+    const int k = r / per_slot;
+    const int j = r - k * per_slot;
+    const int yb = band * w.tyb;
+    const int tb = min(w.tyb, g.ny - yb);
+    int *cnt = w.sync + 1 + band * (g.nz + 2);
+
+    if (j < w.rp) {
+      int p = -1;
+      if (k == 0) { if (w.pre) p = g.nz; }
+      else if (w.pl + (k - 1) <= w.ph) p = w.pl + (k - 1);
+      if (p >= 0) {
+        const int row = j / w.xb, xblk = j - row * w.xb;
+        const int x = xblk * WAVE_SEG + threadIdx.x;
+        if (row <= tb + 1 && x < g.nx) {
+          int y = yb - 1 + row;
+          y = y < 0 ? y + g.ny : (y >= g.ny ? y - g.ny : y);
+          if (w.batch) psi_site<C, PSI, MASK, POL_KEEP, true>(g, fl, x, y, p);
+          else psi_site<C, PSI, MASK, POL_KEEP, false>(g, fl, x, y, p);
+        }
+        __syncwarp();  // the warp's psi stores precede lane 0's release
+        if (lane == 0) red_release_add(cnt + p, 1);
+      }
+    } else if (k > 0) {
+      const int zf = w.z_begin + (k - 1) - w.la;
+      const int jf = j - w.rp;
+      const int row = jf / w.xb, xblk = jf - row * w.xb;
+      if (zf >= w.z_begin && zf < w.z_end && row < tb) {
+        if (lane < 3) {
+          int d = zf + lane - 1;
+          bool need = true;
+          if (d < 1) { need = g.periodic_z_local; d = g.nz; }
+          else if (d > g.nz) { need = g.periodic_z_local; d = 1; }
+          if (need) {
+            const int *c = cnt + d;
+            while (ld_poll(c) < p_target) __nanosleep(32);
+          }
+        }
+        __syncwarp();
+        const int x = xblk * WAVE_SEG + threadIdx.x;
+        if (x < g.nx) fused_site<C, EQ, true, MASK, EXACT, true, POL_STREAM>(g, fl, P, x, yb + row, zf);
+      }
+    }
+
+    // hand-over of the next ticket (item n + 1, slot (n + 1) % RING)
+    const int slot = (n + 1) % WAVE_RING;
+    if (threadIdx.x == 0) {
+      // the slot still holds the ticket of item n + 1 - RING: every warp must have read it
+      if (n + 1 >= WAVE_RING) {
+#pragma unroll
+        for (int i = 1; i < NW; i++) while (prog[i] < n + 1 - WAVE_RING) __nanosleep(40);
+      }
+      ring[slot] = nxt;
+    }
+    int tn;
+    while ((tn = ring[slot]) <= t) __nanosleep(40);  // tickets only grow: a larger value is the new one (no busy spin:
+                                                     // a spinning warp takes issue slots from the working ones)
+    __syncwarp();
+    if (lane == 0) prog[wid] = n + 1;
+    t = tn;
+  }
+}
+
 }  // namespace dlbc
