@@ -1,6 +1,6 @@
 """Run one of the reference's 3-D parameter files through the GPU path -- SURVEY.md 8(f) row 1.
 
-    python -m dlbc_b200.replay case.in [--parameter name=value ...] [--out DIR] [--backend cuda|oracle]
+    python -m dlbc_b200.replay case.in [--parameter name=value ...] [--out DIR]
 
 Plays the role of src/main.d for the lattice-Boltzmann subset: parse the parameter file
 (`dlbc_b200.params`), build mask and initial populations exactly as initMask / initFluids do for a
@@ -10,8 +10,9 @@ the reference's file-name stem, ``<field>-<simulationName>-t%08d`` (io/io.d:157-
 time-stamp id), so they can be compared one to one with ``reference-data/*.h5``; ``--out`` writes them
 as HDF5 files with one contiguous ``/OutArray`` dataset each (`dlbc_b200.h5lite.write_dataset`, 8(f) row 2).
 
-Unsupported parameters fail loudly: electrokinetics, File inits, non-3-D lattices.  The `oracle`
-backend exists for the tests (CPU parity of the driver itself); the product backend is `cuda`.
+Unsupported parameters fail loudly: electrokinetics, File inits, non-3-D lattices.  The timestep always
+runs through libdlbc_cuda (no CPU fallback); `make_lattice` is a seam for the tests, which drive the same
+driver code with their CPU oracle to check the reader and the driver without a GPU.
 """
 from __future__ import annotations
 
@@ -176,29 +177,28 @@ def _collect(L, p, t, out):
         put("mask", L.get_mask())
 
 
-def replay(p, backend="cuda", device=0, arithmetic="fast", kernel="auto"):
-    """Run the case described by parameter dict `p`; returns {file-name stem: array}."""
+def _cuda_lattice(gn, C, kw, device=0, arithmetic="fast", kernel="auto"):
+    from .lattice import Lattice
+    return Lattice(gn, C, **kw, device=device, arithmetic=arithmetic, kernel=kernel)
+
+
+def replay(p, make_lattice=None, **lattice_options):
+    """Run the case described by parameter dict `p`; returns {file-name stem: array}.
+    make_lattice(gn, components, kwargs) -> object with the `Lattice` interface (default: the CUDA library)."""
     gn, C, kw = lattice_kwargs(p)
     names = _fit(p["lb.fieldNames"], C, "lb.lb.fieldNames", strict=True)
     p = dict(p, **{"lb.fieldNames": names})
     blk = I.Block(gn)
     mask = initial_mask(p, blk)
     pops = initial_populations(p, blk, mask)
-    if backend == "cuda":
-        from .lattice import Lattice
-        L = Lattice(gn, C, **kw, device=device, arithmetic=arithmetic, kernel=kernel)
-    elif backend == "oracle":  # tests only
-        from oracle import oracle as O
-        L = O.OracleLattice(gn, C, **kw)
-    else:
-        raise ReplayError(f"unknown backend {backend!r}")
+    L = make_lattice(gn, C, kw) if make_lattice else _cuda_lattice(gn, C, kw, **lattice_options)
     out = {}
     try:
         L.set_mask(mask, halo=blk.halo)
         for c, a in enumerate(pops):
             L.set_populations(c, a, halo=blk.halo)
-        if backend == "oracle":
-            L.exchange_halo()  # main.d:142
+        if hasattr(L, "exchange_halo"):
+            L.exchange_halo()  # main.d:142 (the CUDA library maintains its ghost planes itself)
         _collect(L, p, 0, out)  # "First data dump", main.d:149
         freqs = [p[f"lb.io.{k}Freq"] for k in ("population", "density", "colour", "velocity", "force", "mask")]
         freqs = sorted({f for f in freqs if f > 0})
@@ -209,9 +209,21 @@ def replay(p, backend="cuda", device=0, arithmetic="fast", kernel="auto"):
             t = nxt
             _collect(L, p, t, out)
     finally:
-        if backend == "cuda":
+        if hasattr(L, "close"):
             L.close()
     return out
+
+
+def write_outputs(out, directory, run_id="00000000T000000"):
+    """Write every collected field as the reference would name it (io/io.d:157-172):
+    <field>-<sim>-<run id>-t%08d.h5 with one contiguous /OutArray dataset."""
+    from . import h5lite
+    os.makedirs(directory, exist_ok=True)
+    paths = []
+    for k, v in out.items():
+        stem, t = k.rsplit("-t", 1)
+        paths.append(h5lite.write_dataset(os.path.join(directory, f"{stem}-{run_id}-t{t}.h5"), v))
+    return paths
 
 
 def main(argv=None):
@@ -221,19 +233,15 @@ def main(argv=None):
                     help="override, as the reference's --parameter (repeatable)")
     ap.add_argument("--out", default=None, help="directory for the HDF5 files (/OutArray, the reference's names)")
     ap.add_argument("--run-id", default="00000000T000000", help="time-stamp id in the file names (io/io.d:157-172)")
-    ap.add_argument("--backend", default="cuda", choices=["cuda", "oracle"])
     ap.add_argument("--arith", default="fast", choices=["fast", "exact"])
+    ap.add_argument("--device", type=int, default=0)
     a = ap.parse_args(argv)
     p = P.parse_file(a.parameter_file, a.parameter)
-    out = replay(p, backend=a.backend, arithmetic=a.arith)
-    from . import h5lite
+    out = replay(p, arithmetic=a.arith, device=a.device)
     for k, v in out.items():
         print(f"{k}: shape {v.shape}, sum {float(np.sum(v)):.15g}")
-        if a.out:
-            # the reference's file name (io/io.d:157-172): <field>-<sim>-<run id>-t%08d.h5, dataset /OutArray
-            os.makedirs(a.out, exist_ok=True)
-            stem, t = k.rsplit("-t", 1)
-            h5lite.write_dataset(os.path.join(a.out, f"{stem}-{a.run_id}-t{t}.h5"), v)
+    if a.out:
+        write_outputs(out, a.out, a.run_id)
 
 
 if __name__ == "__main__":

@@ -98,6 +98,12 @@ FAST = {  # the "fast" parameter sets of the reference's test JSON files
 SIM = {"laplace-droplet-3d": "laplace-droplet-3d-gcc3.6"}  # simulationName with its %lb.force.gcc[1][0]% token replaced
 
 
+def _oracle_lattice(gn, C, kw):
+    """The test seam of replay(): the CPU oracle behind the Lattice interface (tests only)."""
+    from oracle import oracle as O
+    return O.OracleLattice(gn, C, **kw)
+
+
 def _check(case, out, g, tol, times):
     """Compare every golden array of `case` at `times` with the replayed output of the same name."""
     n = 0
@@ -124,7 +130,7 @@ def _check(case, out, g, tol, times):
                                             ("bdist2-sc-3d", (0, 10), 1e-15), ("laplace-droplet-3d", (0, 10), 1e-15)])
 def test_replay_reference_case_on_the_oracle(golden, case, times, tol):
     p = P.parse_file(os.path.join(IN, case + ".in"), FAST[case])
-    out = R.replay(p, backend="oracle")
+    out = R.replay(p, make_lattice=_oracle_lattice)
     g = golden(case)
     _check(case, {k: v for k, v in out.items() if k.endswith("t00000000")}, {k: v for k, v in g.items() if k.endswith("-t0")}, 0, (0,))
     _check(case, out, g, tol, times)
@@ -136,7 +142,7 @@ def test_replay_reference_case_on_the_oracle(golden, case, times, tol):
                                         ("bdist2-sc-3d", (0, 10)), ("laplace-droplet-3d", (0, 10))])
 def test_replay_reference_case_on_the_gpu(golden, case, times):
     p = P.parse_file(os.path.join(IN, case + ".in"), FAST[case])
-    out = R.replay(p, backend="cuda")
+    out = R.replay(p)
     _check(case, out, golden(case), "rel", times)
 
 
@@ -144,9 +150,9 @@ def test_replay_reference_case_on_the_gpu(golden, case, times):
 def test_replay_full_length_cases_on_the_gpu(golden):
     """bdist2-sc-3d unmodified (100 steps, populations) and laplace-droplet-3d to t = 100."""
     p = P.parse_file(os.path.join(IN, "bdist2-sc-3d.in"))
-    _check("bdist2-sc-3d", R.replay(p, backend="cuda"), golden("bdist2-sc-3d"), "rel", (0, 100))
+    _check("bdist2-sc-3d", R.replay(p), golden("bdist2-sc-3d"), "rel", (0, 100))
     p = P.parse_file(os.path.join(IN, "laplace-droplet-3d.in"), ["lb.timesteps=100", "lb.io.laplaceFreq=0"])
-    _check("laplace-droplet-3d", R.replay(p, backend="cuda"), golden("laplace-droplet-3d"), "rel", (0, 100))
+    _check("laplace-droplet-3d", R.replay(p), golden("laplace-droplet-3d"), "rel", (0, 100))
 
 
 # ---- HDF5 /OutArray writer (8(f) row 2) --------------------------------------------------------------
@@ -172,10 +178,20 @@ def test_h5_writer_roundtrip_and_layout(tmp_path):
         H.write_dataset(f, np.zeros(3, dtype=np.float32))
 
 
-def test_replay_cli_writes_reference_named_hdf5(tmp_path, golden):
+def test_replay_outputs_as_reference_named_hdf5(tmp_path, golden):
     from dlbc_b200 import h5lite as H
 
-    R.main([os.path.join(IN, "bdist2-3d.in"), "--backend", "oracle", "--out", str(tmp_path), "--run-id", "20260101T000000"])
+    p = P.parse_file(os.path.join(IN, "bdist2-3d.in"))
+    R.write_outputs(R.replay(p, make_lattice=_oracle_lattice), str(tmp_path), "20260101T000000")
     f = tmp_path / "population-red-bdist2-3d-20260101T000000-t00000010.h5"
     assert f.exists()
     assert_bitexact(H.read_dataset(str(f)), golden("bdist2-3d")["population-red-t10"], "population-red t10 from the HDF5 file")
+
+
+@pytest.mark.gpu
+def test_replay_cli_on_the_gpu(tmp_path, golden):
+    from dlbc_b200 import h5lite as H
+
+    R.main([os.path.join(IN, "bdist2-3d.in"), "--arith", "exact", "--out", str(tmp_path), "--run-id", "20260101T000000"])
+    f = tmp_path / "density-blue-bdist2-3d-20260101T000000-t00000010.h5"
+    assert_bitexact(H.read_dataset(str(f)), golden("bdist2-3d")["density-blue-t10"], "density-blue t10 (EXACT arithmetic)")
