@@ -19,6 +19,7 @@ struct dlbc_cuda_ctx {
 
   cudaStream_t compute = nullptr;  // step kernels, layout conversion, host <-> device copies
   cudaStream_t comm = nullptr;     // per-step ghost-plane exchange (NCCL), overlapped with compute
+  cudaStream_t xfer = nullptr;     // host -> staging copies of uploads, overlapped with the layout-conversion kernels
 
   double *f[2] = {nullptr, nullptr};  // populations, A/B: [C][19][sites_g]
   int cur = 0;                        // f[cur] holds the current state
@@ -34,6 +35,9 @@ struct dlbc_cuda_ctx {
   // staging for uploads/downloads/outputs
   void *stage = nullptr;              // device, stage_bytes
   size_t stage_bytes = 0;
+  int stage_half = 0;                 // uploads double-buffer the staging area: half used by the next chunk
+  cudaEvent_t ev_copy = nullptr;      // xfer: chunk copied into its half (the host buffer is free again)
+  cudaEvent_t ev_stage[2] = {nullptr, nullptr};  // compute: the conversion kernel has consumed half i
   double *partial = nullptr;          // device, reduction partials
   int *flags = nullptr;               // device, [2]: bad mask value seen, solid count
   int *wave_sync[3] = {nullptr, nullptr, nullptr};  // wave variant: ticket + counters (interior, lower, upper boundary launch)

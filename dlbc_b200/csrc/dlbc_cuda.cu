@@ -9,6 +9,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -355,21 +356,23 @@ int check_ctx(dlbc_cuda_ctx *ctx) {
 // `host_first` addresses the start (y/z halo included) of the first layer moved; the device side
 // is dense and halo-free, [xc][ny][nz][K].
 template <typename T>
-int copy_layers(dlbc_cuda_ctx *ctx, T *host_first, T *dev_dense, int halo, int K, int64_t xc, bool to_device) {
+int copy_layers(dlbc_cuda_ctx *ctx, T *host_first, T *dev_dense, int halo, int K, int64_t xc, bool to_device,
+                cudaStream_t stream = nullptr) {
   const Geom &g = ctx->g;
+  if (!stream) stream = ctx->compute;
   const int64_t NY = g.ny + 2 * halo, NZ = g.nz + 2 * halo;
   const size_t row = (size_t)g.nz * K * sizeof(T);
   const cudaMemcpyKind kind = to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
   if (halo == 0) {
-    if (to_device) CK(cudaMemcpyAsync((void *)dev_dense, (const void *)host_first, row * g.ny * xc, kind, ctx->compute));
-    else CK(cudaMemcpyAsync((void *)host_first, (const void *)dev_dense, row * g.ny * xc, kind, ctx->compute));
+    if (to_device) CK(cudaMemcpyAsync((void *)dev_dense, (const void *)host_first, row * g.ny * xc, kind, stream));
+    else CK(cudaMemcpyAsync((void *)host_first, (const void *)dev_dense, row * g.ny * xc, kind, stream));
     return 0;
   }
   for (int64_t i = 0; i < xc; i++) {
     T *h = host_first + (i * NY * NZ + (int64_t)halo * NZ + halo) * K;
     T *d = dev_dense + i * g.ny * g.nz * K;
-    if (to_device) CK(cudaMemcpy2DAsync((void *)d, row, (const void *)h, (size_t)NZ * K * sizeof(T), row, g.ny, kind, ctx->compute));
-    else CK(cudaMemcpy2DAsync((void *)h, (size_t)NZ * K * sizeof(T), (const void *)d, row, row, g.ny, kind, ctx->compute));
+    if (to_device) CK(cudaMemcpy2DAsync((void *)d, row, (const void *)h, (size_t)NZ * K * sizeof(T), row, g.ny, kind, stream));
+    else CK(cudaMemcpy2DAsync((void *)h, (size_t)NZ * K * sizeof(T), (const void *)d, row, row, g.ny, kind, stream));
   }
   return 0;
 }
@@ -450,7 +453,9 @@ int dlbc_cuda_destroy(dlbc_cuda_ctx *ctx) {
   if (ctx->stage) cudaFree(ctx->stage);
   if (ctx->flags) cudaFree(ctx->flags);
   for (int *p : ctx->wave_sync) if (p) cudaFree(p);
-  for (cudaEvent_t e : {ctx->ev_a, ctx->ev_b, ctx->ev_bnd, ctx->ev_ghost_psi, ctx->ev_ghost_f}) if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : {ctx->ev_a, ctx->ev_b, ctx->ev_bnd, ctx->ev_ghost_psi, ctx->ev_ghost_f, ctx->ev_copy, ctx->ev_stage[0],
+                        ctx->ev_stage[1]}) if (e) cudaEventDestroy(e);
+  if (ctx->xfer) cudaStreamDestroy(ctx->xfer);
   for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
   for (cudaStream_t s : {ctx->compute, ctx->comm}) if (s) cudaStreamDestroy(s);
   delete ctx;
@@ -544,6 +549,10 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
     CKC(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
     CKC(cudaStreamCreateWithPriority(&ctx->comm, cudaStreamNonBlocking, prio_hi));
   }
+  CKC(cudaStreamCreateWithFlags(&ctx->xfer, cudaStreamNonBlocking));
+  CKC(cudaEventCreateWithFlags(&ctx->ev_copy, cudaEventDisableTiming));
+  CKC(cudaEventCreateWithFlags(&ctx->ev_stage[0], cudaEventDisableTiming));
+  CKC(cudaEventCreateWithFlags(&ctx->ev_stage[1], cudaEventDisableTiming));
   CKC(cudaEventCreate(&ctx->ev_a));
   CKC(cudaEventCreate(&ctx->ev_b));
   CKC(cudaEventCreateWithFlags(&ctx->ev_bnd, cudaEventDisableTiming));
@@ -606,16 +615,29 @@ int dlbc_cuda_upload_populations_xrange(dlbc_cuda_ctx *ctx, int comp, const doub
   const Geom &g = ctx->g;
   TRY(join_comm(ctx));
   const int64_t xcmax = chunk_layers(ctx, Q, sizeof(double));
-  TRY(ensure_stage(ctx, (size_t)xcmax * g.ny * g.nz * Q * sizeof(double)));
-  // `aos` points at layer x_begin of the host array (the first of the layers moved)
+  const int64_t half_elems = xcmax * g.ny * g.nz * Q;
+  TRY(ensure_stage(ctx, (size_t)2 * half_elems * sizeof(double)));
+  // `aos` points at layer x_begin of the host array (the first of the layers moved).
+  // Double-buffered: the host -> staging copy of a chunk (xfer stream) overlaps the layout conversion of
+  // the previous chunk (compute stream), across calls too.  The call returns when the COPY is done, i.e.
+  // when the host buffer may be reused; the conversion kernels stay queued on the compute stream, in
+  // front of whatever the host enqueues next.
   const int64_t NY = g.ny + 2 * halo, NZ = g.nz + 2 * halo;
   for (int64_t x0 = x_begin; x0 < x_begin + x_count; x0 += xcmax) {
     const int64_t xc = std::min(xcmax, x_begin + x_count - x0);
-    TRY(copy_layers<const double>(ctx, aos + (x0 - x_begin) * NY * NZ * Q, (const double *)ctx->stage, halo, Q, xc, true));
-    CK(launch_aos_to_soa(g, (const double *)ctx->stage, (int)xc, (int)x0, comp, ctx->f[ctx->cur], ctx->f[1 - ctx->cur],
-                         ctx->compute));
+    const int h = ctx->stage_half;
+    ctx->stage_half ^= 1;
+    const double *half = (const double *)ctx->stage + (int64_t)h * half_elems;
+    CK(cudaStreamWaitEvent(ctx->xfer, ctx->ev_stage[h], 0));  // the kernel that last read this half is done
+    TRY(copy_layers<const double>(ctx, aos + (x0 - x_begin) * NY * NZ * Q, half, halo, Q, xc, true, ctx->xfer));
+    CK(cudaEventRecord(ctx->ev_copy, ctx->xfer));
+    CK(cudaStreamWaitEvent(ctx->compute, ctx->ev_copy, 0));
+    CK(launch_aos_to_soa(g, half, (int)xc, (int)x0, comp, ctx->f[ctx->cur], ctx->f[1 - ctx->cur], ctx->compute));
     ctx->launches++;
-    CK(cudaStreamSynchronize(ctx->compute));  // the staging area is reused by the next chunk
+    CK(cudaEventRecord(ctx->ev_stage[h], ctx->compute));
+    static const char *e_ov = std::getenv("DLBC_UPLOAD_OVERLAP");
+    if (e_ov && e_ov[0] == '0') CK(cudaStreamSynchronize(ctx->compute));  // measurement: no overlap
+    else CK(cudaEventSynchronize(ctx->ev_copy));
   }
   ctx->ghosts_valid = false;
   ctx->rho_wall_valid = false;
