@@ -568,8 +568,8 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
   CKC(cudaMalloc(&ctx->partial, (size_t)(4 * REDUCE_BLOCKS + 4) * sizeof(double)));
   CKC(cudaMalloc(&ctx->flags, 2 * sizeof(int)));
   for (int i = 0; i < (cfg->nranks > 1 ? 3 : 1); i++) {
-    CKC(cudaMalloc(&ctx->wave_sync[i], wave_sync_ints(g, 1) * sizeof(int)));
-    ctx->device_bytes += (int64_t)(wave_sync_ints(g, 1) * sizeof(int));
+    CKC(cudaMalloc(&ctx->wave_sync[i], wave_sync_alloc_ints(g) * sizeof(int)));
+    ctx->device_bytes += (int64_t)(wave_sync_alloc_ints(g) * sizeof(int));
   }
   ctx->device_bytes += (int64_t)(2 * fbytes + sbytes + g.sites_g + (4 * REDUCE_BLOCKS + 4) * sizeof(double) + 8);
   CKC(cudaMemsetAsync(ctx->f[0], 0, fbytes, ctx->compute));

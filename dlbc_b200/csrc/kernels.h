@@ -14,12 +14,14 @@ struct StepLaunch {
   int *wave_sync;  // ticket + completion counters of the wave variant (wave_sync_ints() ints)
 };
 
-// size of StepLaunch::wave_sync: 1 ticket + one counter per (band, ghost-inclusive plane); sized for
-// the smallest band height the launcher accepts (1 row)
+// size of StepLaunch::wave_sync: 1 ticket + one completion counter per (band, ghost-inclusive plane, row of
+// the band incl. its two halo rows); allocated for the worst case (band height 1: 3 rows per band)
 inline size_t wave_sync_ints(const Geom &g, int tyb) {
   const int nb = (g.ny + tyb - 1) / tyb;
-  return 1 + (size_t)nb * (g.nz + 2);
+  return 1 + (size_t)nb * (g.nz + 2) * (tyb + 2);
 }
+// upper bound of wave_sync_ints over all band heights (ceil(ny / t) * (t + 2) <= 3 ny + 16)
+inline size_t wave_sync_alloc_ints(const Geom &g) { return 1 + (size_t)(3 * g.ny + 16) * (g.nz + 2); }
 
 // z_begin / z_count address ghost-inclusive planes: the physical planes are 1..nz.
 // Each returns cudaGetLastError() of its launch.  One translation unit per (component count,

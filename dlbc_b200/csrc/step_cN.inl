@@ -203,8 +203,12 @@ static cudaError_t wave_launch(const StepLaunch &L, int z_begin, int z_count) {
   if (w.tyb > g.ny) w.tyb = g.ny;
   w.xb = (g.nx + WAVE_SEG - 1) / WAVE_SEG;
   // lag of F behind P: at least 2 slots (F(z) reads psi(z+1)); more when a band-plane is smaller than
-  // the ~80k sites the GPU keeps in flight, so that F blocks rarely have to wait
-  int la = e_la ? std::atoi(e_la) : (int)((81920 + (int64_t)w.tyb * g.nx - 1) / ((int64_t)w.tyb * g.nx));
+  // the ~80k sites the GPU keeps in flight, so that F blocks rarely have to wait.  With per-row completion
+  // counters (rowsync) an F item only waits for the 9 row segments it reads, and one slot less is best
+  // (512^2 planes, TYB = 32: LA 4 with rowsync 6.96 GLUPS, LA 5 without 6.81; profiles/README.md).
+  static const char *e_rs0 = std::getenv("DLBC_WAVE_ROWSYNC");
+  const int64_t lag_sites = (e_rs0 ? std::atoi(e_rs0) : 1) ? 65536 : 81920;
+  int la = e_la ? std::atoi(e_la) : (int)((lag_sites + (int64_t)w.tyb * g.nx - 1) / ((int64_t)w.tyb * g.nx));
   if (la < 2) la = 2;
   if (!e_la && la > 8) la = 8;
   w.la = la;
@@ -232,6 +236,8 @@ static cudaError_t wave_launch(const StepLaunch &L, int z_begin, int z_count) {
   w.pf = e_pf ? std::atoi(e_pf) : 0;   // measured slower when on (profiles/r01_wave_experiments.md): L2 capacity, not latency, is the limit
   w.pf_keep = e_pfk ? std::atoi(e_pfk) : 1;
   static const char *e_batch = std::getenv("DLBC_WAVE_BATCH");
+  static const char *e_rs = std::getenv("DLBC_WAVE_ROWSYNC");
+  w.rowsync = e_rs ? std::atoi(e_rs) : 1;
   w.batch = e_batch ? std::atoi(e_batch) : 1;  // with LA = 5: +2-4 % (LA = 4: -8 %), profiles/README.md
   static const char *e_free = std::getenv("DLBC_WAVE_FREE");  // 1: barrier-free form (wave_free_kernel)
   if (!SPLIT && (e_free ? std::atoi(e_free) != 0 : false)) {

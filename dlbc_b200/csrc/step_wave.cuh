@@ -43,7 +43,8 @@ struct Wave {
   int pf;              // L2 prefetch distance in tickets (0 = off): see wave_prefetch
   int pf_keep;         // prefetch with L2::evict_last (else default priority)
   int batch;           // P items gather all components before summing (psi_site BATCH)
-  int *sync;           // [0] ticket, [1 + band * (nz + 2) + plane] completed P blocks
+  int rowsync;         // F items wait for the 9 (plane, row) counters they read instead of 3 whole planes
+  int *sync;           // [0] ticket, [1 + ((band * (nz + 2) + plane) * (tyb + 2) + row)] completed P blocks of that row
 };
 
 // Polling load of a completion counter.  relaxed.gpu (LDG.STRONG.GPU) rather than acquire.gpu: an
@@ -302,7 +303,8 @@ wave_kernel(Geom g, Fields fl, StepParams P, Wave w) {
     const int j = r - k * per_slot;
     const int yb = band * w.tyb;
     const int tb = min(w.tyb, g.ny - yb);   // rows of this (possibly ragged) band
-    int *cnt = w.sync + 1 + band * (g.nz + 2);
+    const int rows = w.tyb + 2;
+    int *cnt = w.sync + 1 + (int64_t)band * (g.nz + 2) * rows;  // [plane][row]
 
     if (j < w.rp) {
       // ---- P item: psi of one row segment of plane p
@@ -320,7 +322,7 @@ wave_kernel(Geom g, Fields fl, StepParams P, Wave w) {
           else psi_site<C, PSI, MASK, POL_KEEP, false>(g, fl, x, y, p);
         }
         __syncthreads();  // all psi stores of the block precede (CTA scope) the lead thread's release below
-        if (lead) red_release_add(cnt + p, 1);
+        if (lead) red_release_add(cnt + p * rows + row, 1);
       }
     } else if (k > 0) {
       // ---- F item: fused update of one row segment of plane zf
@@ -328,14 +330,21 @@ wave_kernel(Geom g, Fields fl, StepParams P, Wave w) {
       const int jf = j - w.rp;
       const int row = jf / w.xb, xblk = jf - row * w.xb;
       if (zf >= w.z_begin && zf < w.z_end && row < tb) {
-        if (threadIdx.x < 3 && comp == 0) {
-          int d = zf + (int)threadIdx.x - 1;
-          bool need = true;
-          if (d < 1) { need = g.periodic_z_local; d = g.nz; }
-          else if (d > g.nz) { need = g.periodic_z_local; d = 1; }
-          if (need) {
-            const int *c = cnt + d;
-            while (ld_poll(c) < w.rp) __nanosleep(32);
+        // psi of planes zf-1..zf+1, rows y-1..y+1 (P rows row..row+2 of this band), all x segments of those
+        // rows (xb items each): 9 counters, or -- rowsync off -- every row of the 3 planes
+        const int nwait = w.rowsync ? 9 : 3 * (tb + 2);
+        if (comp == 0) {
+          for (int i = threadIdx.x; i < nwait; i += WAVE_SEG) {
+            const int i3 = w.rowsync ? i / 3 : i / (tb + 2);
+            const int rr = w.rowsync ? row + i % 3 : i % (tb + 2);
+            int d = zf + i3 - 1;
+            bool need = true;
+            if (d < 1) { need = g.periodic_z_local; d = g.nz; }
+            else if (d > g.nz) { need = g.periodic_z_local; d = 1; }
+            if (need) {
+              const int *c = cnt + d * rows + rr;
+              while (ld_poll(c) < w.xb) __nanosleep(32);
+            }
           }
         }
         __syncthreads();
@@ -379,7 +388,6 @@ wave_free_kernel(Geom g, Fields fl, StepParams P, Wave w) {
   const int per_slot = w.rp + w.rf;
   const int per_band = w.slots * per_slot;
   const int total = w.nbands * per_band;
-  const int p_target = w.rp * NW;
   if (threadIdx.x == 0) ring[0] = atomicAdd(w.sync, 1);
   else if (threadIdx.x < WAVE_RING) ring[threadIdx.x] = -1;
   if (threadIdx.x < NW) prog[threadIdx.x] = 0;
@@ -395,7 +403,8 @@ wave_free_kernel(Geom g, Fields fl, StepParams P, Wave w) {
     const int j = r - k * per_slot;
     const int yb = band * w.tyb;
     const int tb = min(w.tyb, g.ny - yb);
-    int *cnt = w.sync + 1 + band * (g.nz + 2);
+    const int rows = w.tyb + 2;
+    int *cnt = w.sync + 1 + (int64_t)band * (g.nz + 2) * rows;  // [plane][row]
 
     if (j < w.rp) {
       int p = -1;
@@ -411,21 +420,21 @@ wave_free_kernel(Geom g, Fields fl, StepParams P, Wave w) {
           else psi_site<C, PSI, MASK, POL_KEEP, false>(g, fl, x, y, p);
         }
         __syncwarp();  // the warp's psi stores precede lane 0's release
-        if (lane == 0) red_release_add(cnt + p, 1);
+        if (lane == 0) red_release_add(cnt + p * rows + row, 1);
       }
     } else if (k > 0) {
       const int zf = w.z_begin + (k - 1) - w.la;
       const int jf = j - w.rp;
       const int row = jf / w.xb, xblk = jf - row * w.xb;
       if (zf >= w.z_begin && zf < w.z_end && row < tb) {
-        if (lane < 3) {
-          int d = zf + lane - 1;
+        if (lane < 9) {
+          int d = zf + lane / 3 - 1;
           bool need = true;
           if (d < 1) { need = g.periodic_z_local; d = g.nz; }
           else if (d > g.nz) { need = g.periodic_z_local; d = 1; }
           if (need) {
-            const int *c = cnt + d;
-            while (ld_poll(c) < p_target) __nanosleep(32);
+            const int *c = cnt + d * rows + row + lane % 3;
+            while (ld_poll(c) < w.xb * NW) __nanosleep(32);
           }
         }
         __syncwarp();
