@@ -289,22 +289,27 @@ int step_once(dlbc_cuda_ctx *ctx, KernelTimer *kt) {
     ctx->launches++;
     if (kt) kt->end();
   } else if (single_pass) {
-    // z-slab ring, single-pass kernel.  The interior planes 2..nz-1 need nothing from this step's
-    // exchanges (psi of planes 1 and nz is computed inside the kernel from populations whose ghost
-    // planes arrived at the end of the previous step), so they run on the compute stream while
-    // the high-priority comm stream runs the boundary chain: psi of planes 1 and nz -> NCCL psi
-    // ghost exchange -> planes 1 and nz -> NCCL exchange of the 5 crossing populations per side.
-    StepLaunch Lb = make_launch(ctx, ctx->comm), Lb2 = make_launch(ctx, ctx->comm);
+    // z-slab ring, single-pass kernel.  The interior launch is persistent (it fills every SM until it
+    // ends), so anything queued beside it starves: the boundary work therefore runs FIRST on the compute
+    // stream -- psi of planes 1 and nz -> [comm: NCCL psi ghost exchange] -> planes 1 and nz -- and only the
+    // exchange of the 5 crossing populations per side overlaps the interior planes 2..nz-1, which need
+    // nothing from this step's exchanges (they recompute psi of planes 1 and nz from populations whose
+    // ghost planes arrived at the end of the previous step).
+    StepLaunch Lb = make_launch(ctx, ctx->compute), Lb2 = make_launch(ctx, ctx->compute);
     Lb.wave_sync = ctx->wave_sync[1];
     Lb2.wave_sync = ctx->wave_sync[2];
     CK(cudaStreamWaitEvent(ctx->compute, ctx->ev_ghost_f, 0));
+    CK(K.psi(L, 1, 1)); ctx->launches++;
+    if (nz > 1) { CK(K.psi(L, nz, 1)); ctx->launches++; }
     CK(cudaEventRecord(ctx->ev_bnd, ctx->compute));
     CK(cudaStreamWaitEvent(ctx->comm, ctx->ev_bnd, 0));
-    CK(K.psi(Lb, 1, 1)); ctx->launches++;
-    if (nz > 1) { CK(K.psi(Lb, nz, 1)); ctx->launches++; }
     TRY(exchange_planes<double>(ctx, scalar_xfer(ctx, ctx->psi, ctx->cfg.ncomp), ncclDouble, ctx->comm));
+    CK(cudaEventRecord(ctx->ev_ghost_psi, ctx->comm));
+    CK(cudaStreamWaitEvent(ctx->compute, ctx->ev_ghost_psi, 0));
     CK(fused(Lb, 1, 1)); ctx->launches++;
     if (nz > 1) { CK(fused(Lb2, nz, 1)); ctx->launches++; }
+    CK(cudaEventRecord(ctx->ev_bnd, ctx->compute));
+    CK(cudaStreamWaitEvent(ctx->comm, ctx->ev_bnd, 0));
     TRY(exchange_planes<double>(ctx, population_xfer(ctx, ctx->f[1 - ctx->cur]), ncclDouble, ctx->comm));
     CK(cudaEventRecord(ctx->ev_ghost_f, ctx->comm));
     if (nz > 2) { CK(fused(L, 2, nz - 2)); ctx->launches++; }
