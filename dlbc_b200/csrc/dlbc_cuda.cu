@@ -538,10 +538,12 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
   }
   for (int d = 0; d < 3; d++) p.gacc[d] = cfg->global_acc[d];
 
-  // AUTO: the L2-ordered single launch on one GPU (fastest measured, profiles/README.md); the two-kernel
-  // schedule on z-slabs, where its boundary/interior split overlaps both exchanges with compute
+  // AUTO: the L2-ordered single launch (fastest measured, profiles/README.md), on z-slabs too unless the
+  // slab is thin: its two extra boundary launches cost ~0.4 ms per step at 512^2 planes, which the
+  // two-kernel schedule wins back below ~128 planes (2 GPUs: nz = 64 2.64 vs 2.81 ms, 128 equal,
+  // 256 10.15 vs 10.48 ms, 512 19.6 vs 20.7 ms)
   ctx->variant = cfg->kernel_variant != DLBC_KERNEL_AUTO ? cfg->kernel_variant
-                 : (cfg->nranks == 1 ? DLBC_KERNEL_WAVE : DLBC_KERNEL_TWO_PASS);
+                 : (cfg->nranks == 1 || ctx->g.nz >= 160 ? DLBC_KERNEL_WAVE : DLBC_KERNEL_TWO_PASS);
   if (!cfg->enable_shan_chen) ctx->variant = DLBC_KERNEL_TWO_PASS;
   if (cfg->nranks > 1 && ctx->variant == DLBC_KERNEL_ZMARCH) ctx->variant = DLBC_KERNEL_TWO_PASS;  // no ghost-psi path
   if (cfg->ncomp > 2 && ctx->variant != DLBC_KERNEL_WAVE)

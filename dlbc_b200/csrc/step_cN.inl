@@ -214,7 +214,8 @@ static cudaError_t wave_launch(const StepLaunch &L, int z_begin, int z_count) {
   w.la = la;
   w.rp = (w.tyb + 2) * w.xb;
   w.rf = w.tyb * w.xb;
-  const int np = w.ph - w.pl + 1, nf = z_count + w.la;
+  // F(zf) runs in slot zf - pl + 1 + la (step_wave.cuh); the last one is zf = z_end - 1
+  const int np = w.ph - w.pl + 1, nf = (w.z_end - 1 - w.pl + 1) + w.la;
   w.slots = 1 + (np > nf ? np : nf);
   w.nbands = (g.ny + w.tyb - 1) / w.tyb;
   w.sync = L.wave_sync;

@@ -13,7 +13,8 @@
 //     P(p):  psi of plane p for rows yb-1 .. yb+TYB (the band plus a one-row halo, recomputed by
 //            the neighbouring band too: 2/TYB extra psi work, deterministic, identical bits)
 //     F(z):  fused pull + Shan-Chen force + collide of plane z, rows yb .. yb+TYB-1
-// with F(z) scheduled LA planes behind P(z + LA) (band-plane = TYB * nx sites, ~5-10 MB).
+// with F(z) scheduled LA slots behind P(z), i.e. in the slot of P(z + LA) (band-plane = TYB * nx sites,
+// ~5-10 MB).
 //
 // Ordering without a grid barrier: every block takes a ticket (atomicAdd) when it starts and
 // derives its work item from the ticket, so "earlier ticket" == "already running or finished".
@@ -326,7 +327,7 @@ wave_kernel(Geom g, Fields fl, StepParams P, Wave w) {
       }
     } else if (k > 0) {
       // ---- F item: fused update of one row segment of plane zf
-      const int zf = w.z_begin + (k - 1) - w.la;
+      const int zf = w.pl + (k - 1) - w.la;  // `la` slots behind the P item of the same plane (pl < z_begin on slabs)
       const int jf = j - w.rp;
       const int row = jf / w.xb, xblk = jf - row * w.xb;
       if (zf >= w.z_begin && zf < w.z_end && row < tb) {
@@ -423,7 +424,7 @@ wave_free_kernel(Geom g, Fields fl, StepParams P, Wave w) {
         if (lane == 0) red_release_add(cnt + p * rows + row, 1);
       }
     } else if (k > 0) {
-      const int zf = w.z_begin + (k - 1) - w.la;
+      const int zf = w.pl + (k - 1) - w.la;  // `la` slots behind the P item of the same plane (pl < z_begin on slabs)
       const int jf = j - w.rp;
       const int row = jf / w.xb, xblk = jf - row * w.xb;
       if (zf >= w.z_begin && zf < w.z_end && row < tb) {
