@@ -172,6 +172,98 @@ def pinned_array(lib, shape):
     return np.frombuffer(buf, dtype=np.float64).reshape(shape), ptr
 
 
+def _bitwise_equal(a, b):
+    return a.shape == b.shape and bool((a.view(np.uint64) == b.view(np.uint64)).all())
+
+
+def parity_check(args, device):
+    """Driver-visible parity evidence for the kernel the bench times: on a 512 x 512 x 64 lattice (the band /
+    segment / lag geometry of the single-launch kernels depends on nx, ny only, so this IS the 512^3 regime:
+    16 bands of 32 rows, 8 (TMA) or 4 (wave) x-segments per row, lag 4, every SM busy) step the SAME uploaded
+    state a few times with the benchmarked kernel, the register-path wave kernel and the two-kernel schedule
+    and compare the downloaded populations bit for bit (same site functions => identical bits)."""
+    from dlbc_b200 import cases, init as I
+    from dlbc_b200.lattice import Lattice
+    gn = (args.size, args.size, 64) if not args.shape else tuple(int(v) for v in args.shape.split(","))[:2] + (64,)
+    if args.components != 2:
+        return None
+    steps, xc = 4, 32
+    layers = [cases.synthetic_layers(gn, xc, 0.37, 0.02, I.BDIST2, 1000 + k) for k in range(3)]
+    kernels = [args.kernel, "wave", "two_pass"] if args.kernel != "two_pass" else ["two_pass", "wave"]
+    ctxs, names = [], []
+    try:
+        for k in kernels:
+            G = Lattice(gn, 2, **cases.SC2, arithmetic=args.arith, kernel=k, device=device)
+            for c in range(2):
+                for i, x0 in enumerate(range(0, gn[0], xc)):
+                    G.set_populations_xrange(c, layers[(c + i) % 3][: min(xc, gn[0] - x0)], x0)
+            names.append(G.kernel_variant)
+            G.step(steps)
+            ctxs.append(G)
+        same, checked = True, 0
+        for c in range(2):
+            for x0 in range(0, gn[0], 64):
+                cnt = min(64, gn[0] - x0)
+                ref = ctxs[-1].get_populations_xrange(c, x0, cnt)
+                for G in ctxs[:-1]:
+                    same = same and _bitwise_equal(G.get_populations_xrange(c, x0, cnt), ref)
+                checked += ref.size
+        finite = bool(np.isfinite(ref).all())
+    finally:
+        for G in ctxs:
+            G.close()
+    return {"bitexact": bool(same and finite), "kernels": names, "lattice": list(gn), "steps": steps,
+            "arithmetic": args.arith, "values_compared": int(checked)}
+
+
+def decomposition_check(args, dist, rank, world, local_rank, dlib):
+    """Driver-visible multi-GPU correctness (the reference runs every test on several process grids against one
+    golden, tests/runnable/dlbct/run.py:28-30): the same case on the N-rank NCCL communicator and on ONE rank
+    must give bit-identical populations (EXACT arithmetic; the per-site arithmetic does not depend on the
+    split).  Two cases: thin slabs (AUTO -> two-kernel schedule) and slabs of 160 planes (AUTO -> the
+    single-launch kernel, forced into several bands)."""
+    import torch
+    from dlbc_b200 import slabs
+    from dlbc_b200.lattice import Lattice
+    from dlbc_b200 import cases, init as I
+    out = {}
+    for name, planes, opts in (("thin_slabs", 32, {}), ("thick_slabs", 160, {"wave_tyb": 12})):
+        gn = (64, 48, planes * world)
+        rngs = [np.random.default_rng(77 + c) for c in range(2)]
+        pops = [(r0 + 0.05 * g.random(gn))[..., None] * I.eq_dist_unity(cases.d3q19, I.BDIST2)
+                for r0, g in zip((0.6, 0.12), rngs)]
+        steps = 6
+        nccl_id = slabs.broadcast_unique_id(dist, rank, dlib.nccl_unique_id, dlib.NCCL_ID_BYTES, device="cuda")
+        z0, z1 = slabs.slab_range(gn[2], rank, world)
+        with Lattice(gn, 2, **cases.SC2, global_acc=[1e-5, 0, -1e-5], arithmetic="exact", kernel="auto",
+                     device=local_rank, rank=rank, nranks=world, nccl_id=nccl_id) as G:
+            variant = G.kernel_variant
+            for k, v in opts.items():
+                G.set_option(k, v)
+            for c in range(2):
+                G.set_populations(c, np.ascontiguousarray(pops[c][:, :, z0:z1]))
+            G.step(steps)
+            mine = [G.get_populations(c) for c in range(2)]
+        ref = torch.empty((2,) + gn + (19,), dtype=torch.float64, device="cuda")
+        if rank == 0:
+            with Lattice(gn, 2, **cases.SC2, global_acc=[1e-5, 0, -1e-5], arithmetic="exact", kernel="two_pass",
+                         device=local_rank) as G1:
+                for c in range(2):
+                    G1.set_populations(c, pops[c])
+                G1.step(steps)
+                for c in range(2):
+                    ref[c].copy_(torch.from_numpy(G1.get_populations(c)))
+        dist.broadcast(ref, 0)
+        ok = all(_bitwise_equal(mine[c], np.ascontiguousarray(ref[c, :, :, z0:z1].cpu().numpy())) for c in range(2))
+        t = torch.tensor([1 if ok else 0], dtype=torch.int32, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        out[name] = {"bitexact": bool(t.item() == 1), "kernel": variant, "lattice": list(gn), "steps": steps,
+                     "reference": "two_pass on 1 rank"}
+        del ref
+    out["bitexact"] = all(v["bitexact"] for v in out.values())
+    return out
+
+
 def run_ours(args, rank, world, local_rank):
     from dlbc_b200 import cases, init as I
     from dlbc_b200 import lib as dlib
@@ -186,6 +278,11 @@ def run_ours(args, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         from dlbc_b200 import slabs
         nccl_id = slabs.broadcast_unique_id(dist, rank, dlib.nccl_unique_id, dlib.NCCL_ID_BYTES, device="cuda")
+
+    decomp = None
+    if world > 1 and not args.no_checks:
+        decomp = decomposition_check(args, dist, rank, world, local_rank, dlib)
+        log(f"rank {rank}: decomposition check {decomp}")
 
     n = args.size
     ncomp = args.components
@@ -318,9 +415,15 @@ def run_ours(args, rank, world, local_rank):
         lib.dlbc_cuda_host_free(dptr)
 
     mass = [G.total_mass(c) for c in range(ncomp)]
+    variant = G.kernel_variant
     G.close()
     for p in ptrs:
         lib.dlbc_cuda_host_free(p)
+
+    parity = None
+    if world == 1 and not args.no_checks and not porous:
+        parity = parity_check(args, local_rank)
+        log(f"parity check {parity}")
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -341,7 +444,7 @@ def run_ours(args, rank, world, local_rank):
                        "arithmetic": args.arith, "kernel": args.kernel,
                        "l2": "inputs exceed L2 (populations are %.1f GB per GPU)" % (2 * ncomp * 19 * 8 * sites_local / 1e9)},
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-            "total_mass": mass,
+            "total_mass": mass, "kernel_variant": variant, "parity_check": parity, "decomposition_invariant": decomp,
         }
         print(json.dumps(line), flush=True)
     if dist is not None:
@@ -363,11 +466,13 @@ def main():
     ap.add_argument("--workload", default="spinodal", choices=["spinodal", "porous"],
                     help="porous: BASELINE configs[3] (mask-heavy path), device-resident timing only")
     ap.add_argument("--arith", default="fast", choices=["fast", "exact"])
-    ap.add_argument("--kernel", default="auto", choices=["auto", "two_pass", "zmarch", "zpipe", "wave"])
+    ap.add_argument("--kernel", default="auto", choices=["auto", "two_pass", "wave", "tma"])
     ap.add_argument("--cpu-sample", type=int, default=128)
     ap.add_argument("--cpu-steps", type=int, default=20)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-checks", action="store_true",
+                    help="skip the parity check (N = 1) / the decomposition-invariance check (N > 1)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -375,6 +480,13 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if world != args.gpus and world > 1:
         log(f"note: WORLD_SIZE={world} but --gpus {args.gpus}; using WORLD_SIZE")
+    if args.gpus > 1 and "WORLD_SIZE" not in os.environ:
+        # `python bench.py --gpus N` without a launcher: start the N ranks ourselves (one process per GPU)
+        port = 29500 + os.getpid() % 2000
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.abspath(__file__)] + sys.argv[1:]
+        log("re-launching under torch.distributed.run:", " ".join(cmd))
+        raise SystemExit(subprocess.call(cmd))
     if args.impl == "reference":
         run_reference(args, rank)
     else:

@@ -15,7 +15,9 @@ struct dlbc_cuda_ctx {
   dlbc::Geom g{};
   dlbc::StepParams p{};
   int device = 0;
-  int variant = DLBC_KERNEL_TWO_PASS;
+  int variant = DLBC_KERNEL_TWO_PASS;  // requested / AUTO-resolved variant (effective_variant() applies the TMA size rule)
+  bool variant_auto = false;
+  int opt_wave_tyb = 0, opt_wave_la = 0;  // dlbc_cuda_set_option
 
   cudaStream_t compute = nullptr;  // step kernels, layout conversion, host <-> device copies
   cudaStream_t comm = nullptr;     // per-step ghost-plane exchange (NCCL), overlapped with compute

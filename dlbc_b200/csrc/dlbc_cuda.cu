@@ -27,16 +27,14 @@ struct KernelSet {
   launch_fn psi;
   force_fn force;
   launch_fn fused[2];   // [exact]
-  launch_fn zmarch[2];  // [exact]
-  launch_fn zpipe[2];   // [exact]
   launch_fn wave[2];    // [exact]
+  launch_fn tma[2];     // [exact]
 };
 
 #define DLBC_SET(NC)                                                                                      \
   { launch_psi_c##NC, launch_force_c##NC, {launch_fused_fast_c##NC, launch_fused_exact_c##NC},            \
-    {launch_zmarch_fast_c##NC, launch_zmarch_exact_c##NC},                                                \
-    {launch_zpipe_fast_c##NC, launch_zpipe_exact_c##NC},                                                  \
-    {launch_wave_fast_c##NC, launch_wave_exact_c##NC} }
+    {launch_wave_fast_c##NC, launch_wave_exact_c##NC},                                                    \
+    {launch_tma_fast_c##NC, launch_tma_exact_c##NC} }
 const KernelSet kKernels[DLBC_CUDA_MAX_COMPONENTS] = {DLBC_SET(1), DLBC_SET(2), DLBC_SET(3), DLBC_SET(4)};
 #undef DLBC_SET
 
@@ -121,6 +119,8 @@ StepLaunch make_launch(dlbc_cuda_ctx *ctx, cudaStream_t s) {
   L.mask = ctx->has_solid ? 1 : 0;
   L.stream = s;
   L.wave_sync = ctx->wave_sync[0];
+  L.wave_tyb = ctx->opt_wave_tyb;
+  L.wave_la = ctx->opt_wave_la;
   return L;
 }
 
@@ -261,21 +261,25 @@ struct KernelTimer {
   }
 };
 
+// The TMA variant moves rows in 16-byte units: nx must be even, and a multiple of 4 once solid sites exist
+// (4-byte neighbourhood words).  AUTO falls back to the register path; an explicit request fails in step().
+bool tma_ok(const dlbc_cuda_ctx *ctx) { return ctx->g.nx % (ctx->has_solid ? 4 : 2) == 0; }
+int effective_variant(const dlbc_cuda_ctx *ctx) {
+  if (ctx->variant == DLBC_KERNEL_TMA && ctx->variant_auto && !tma_ok(ctx)) return DLBC_KERNEL_WAVE;
+  return ctx->variant;
+}
+
 // One timestep: the statements of runTimeloop, main.d:179-195.
 int step_once(dlbc_cuda_ctx *ctx, KernelTimer *kt) {
   const KernelSet &K = kKernels[ctx->cfg.ncomp - 1];
   const int exact = ctx->cfg.arithmetic == DLBC_ARITH_EXACT ? 1 : 0;
   const int nz = ctx->g.nz;
   const bool sc = ctx->cfg.enable_shan_chen != 0;
-  const bool single_pass = ctx->variant == DLBC_KERNEL_ZMARCH || ctx->variant == DLBC_KERNEL_ZPIPE ||
-                           ctx->variant == DLBC_KERNEL_WAVE;
+  const int variant = effective_variant(ctx);
+  const bool single_pass = variant == DLBC_KERNEL_WAVE || variant == DLBC_KERNEL_TMA;
   StepLaunch L = make_launch(ctx, ctx->compute);
-  launch_fn fused = ctx->variant == DLBC_KERNEL_WAVE ? K.wave[exact]
-                    : ctx->variant == DLBC_KERNEL_ZPIPE ? K.zpipe[exact]
-                    : ctx->variant == DLBC_KERNEL_ZMARCH ? K.zmarch[exact] : K.fused[exact];
-  const char *fused_name = ctx->variant == DLBC_KERNEL_WAVE ? "wave_kernel"
-                           : ctx->variant == DLBC_KERNEL_ZPIPE ? "zpipe_kernel"
-                           : ctx->variant == DLBC_KERNEL_ZMARCH ? "zmarch_kernel" : "fused_kernel";
+  launch_fn fused = variant == DLBC_KERNEL_TMA ? K.tma[exact] : variant == DLBC_KERNEL_WAVE ? K.wave[exact] : K.fused[exact];
+  const char *fused_name = variant == DLBC_KERNEL_TMA ? "tma_kernel" : variant == DLBC_KERNEL_WAVE ? "wave_kernel" : "fused_kernel";
 
   if (ctx->cfg.nranks == 1) {
     if (sc && !single_pass) {
@@ -481,7 +485,7 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
   ARG(cfg->psi_form == DLBC_PSI_LINEAR || cfg->psi_form == DLBC_PSI_EXPONENTIAL, "create: bad psi_form");
   ARG(cfg->eqdist_form >= 0 && cfg->eqdist_form <= 2, "create: bad eqdist_form");
   ARG(cfg->arithmetic == DLBC_ARITH_FAST || cfg->arithmetic == DLBC_ARITH_EXACT, "create: bad arithmetic mode");
-  ARG(cfg->kernel_variant >= DLBC_KERNEL_AUTO && cfg->kernel_variant <= DLBC_KERNEL_WAVE, "create: bad kernel_variant");
+  ARG(cfg->kernel_variant >= DLBC_KERNEL_AUTO && cfg->kernel_variant <= DLBC_KERNEL_TMA, "create: bad kernel_variant");
   for (int c = 0; c < cfg->ncomp; c++) ARG(cfg->tau[c] > 0.0 && std::isfinite(cfg->tau[c]), "create: tau must be positive");
 
   int ndev = 0;
@@ -538,16 +542,13 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
   }
   for (int d = 0; d < 3; d++) p.gacc[d] = cfg->global_acc[d];
 
-  // AUTO: the L2-ordered single launch (fastest measured, profiles/README.md), on z-slabs too unless the
-  // slab is thin: its two extra boundary launches cost ~0.4 ms per step at 512^2 planes, which the
-  // two-kernel schedule wins back below ~128 planes (2 GPUs: nz = 64 2.64 vs 2.81 ms, 128 equal,
-  // 256 10.15 vs 10.48 ms, 512 19.6 vs 20.7 ms)
-  ctx->variant = cfg->kernel_variant != DLBC_KERNEL_AUTO ? cfg->kernel_variant
-                 : (cfg->nranks == 1 || ctx->g.nz >= 160 ? DLBC_KERNEL_WAVE : DLBC_KERNEL_TWO_PASS);
-  if (!cfg->enable_shan_chen) ctx->variant = DLBC_KERNEL_TWO_PASS;
-  if (cfg->nranks > 1 && ctx->variant == DLBC_KERNEL_ZMARCH) ctx->variant = DLBC_KERNEL_TWO_PASS;  // no ghost-psi path
-  if (cfg->ncomp > 2 && ctx->variant != DLBC_KERNEL_WAVE)
-    ctx->variant = DLBC_KERNEL_TWO_PASS;  // z-march kernels: 19 C doubles per thread must stay in registers
+  // AUTO: the L2-ordered single launch fed by TMA (fastest measured, profiles/README.md), on z-slabs too unless
+  // the slab is thin: its two extra boundary launches cost ~0.4 ms per step at 512^2 planes, which the
+  // two-kernel schedule wins back below ~128 planes
+  ctx->variant_auto = cfg->kernel_variant == DLBC_KERNEL_AUTO;
+  ctx->variant = !ctx->variant_auto ? cfg->kernel_variant
+                 : (cfg->nranks == 1 || ctx->g.nz >= 160 ? DLBC_KERNEL_TMA : DLBC_KERNEL_TWO_PASS);
+  if (!cfg->enable_shan_chen) ctx->variant = DLBC_KERNEL_TWO_PASS;  // nothing to order: one fused kernel per step
 
   CKC(cudaStreamCreateWithFlags(&ctx->compute, cudaStreamNonBlocking));
   {
@@ -729,6 +730,11 @@ int dlbc_cuda_upload_mask(dlbc_cuda_ctx *ctx, const int32_t *mask, int halo) {
     }
     CK(launch_neighbour_bits(g, ctx->mask, ctx->nbmask, ctx->compute));
     ctx->launches++;
+    // a mask that arrives after the populations (or after some steps): make the static values of the solid
+    // sites agree in both buffers (the ghost planes of f[cur] are refreshed first)
+    TRY(ensure_ghosts(ctx));
+    CK(launch_sync_solid(g, ctx->mask, ctx->f[ctx->cur], ctx->f[1 - ctx->cur], ctx->compute));
+    ctx->launches++;
   }
   ctx->rho_wall_valid = false;
   ctx->force_valid = false;
@@ -754,6 +760,8 @@ int dlbc_cuda_step(dlbc_cuda_ctx *ctx, int nsteps) {
   TRY(check_ctx(ctx));
   ARG(nsteps >= 0, "step: negative step count");
   if (nsteps == 0) return 0;
+  ARG(effective_variant(ctx) != DLBC_KERNEL_TMA || tma_ok(ctx),
+      "step: the TMA kernel needs an even nx (a multiple of 4 with solid sites); use AUTO or WAVE");
   TRY(ensure_ghosts(ctx));
   if (ctx->cfg.nranks > 1 && ctx->timestep == 0) CK(cudaEventRecord(ctx->ev_ghost_f, ctx->compute));
   for (int i = 0; i < nsteps; i++) TRY(step_once(ctx, nullptr));
@@ -883,9 +891,28 @@ int dlbc_cuda_device_bytes(const dlbc_cuda_ctx *ctx, int64_t *bytes) {
   return 0;
 }
 
+int dlbc_cuda_kernel_variant(const dlbc_cuda_ctx *ctx, int *variant) {
+  if (!ctx || !variant) return 1;
+  *variant = effective_variant(ctx);
+  return 0;
+}
+
+int dlbc_cuda_set_option(dlbc_cuda_ctx *ctx, const char *name, int64_t value) {
+  TRY(check_ctx(ctx));
+  ARG(name, "set_option: null name");
+  ARG(value >= 0 && value <= 65535, "set_option: value out of range");
+  if (!std::strcmp(name, "wave_tyb")) ctx->opt_wave_tyb = (int)value;
+  else if (!std::strcmp(name, "wave_la")) {
+    ARG(value == 0 || value >= 2, "set_option: wave_la must be >= 2 (a fused item reads psi of the next plane)");
+    ctx->opt_wave_la = (int)value;
+  } else return set_error(ctx, std::string("dlbc_cuda: set_option: unknown option ") + name, 1);
+  return 0;
+}
+
 int dlbc_cuda_timed_steps(dlbc_cuda_ctx *ctx, int nsteps, double *elapsed_ms) {
   TRY(check_ctx(ctx));
   ARG(nsteps >= 0 && elapsed_ms, "timed_steps: bad argument");
+  ARG(effective_variant(ctx) != DLBC_KERNEL_TMA || tma_ok(ctx), "timed_steps: the TMA kernel needs an even nx");
   TRY(ensure_ghosts(ctx));
   if (ctx->cfg.nranks > 1 && ctx->timestep == 0) CK(cudaEventRecord(ctx->ev_ghost_f, ctx->compute));
   TRY(join_comm(ctx));

@@ -156,6 +156,27 @@ cudaError_t launch_neighbour_bits(const Geom &g, const uint8_t *m, uint32_t *nb,
   return cudaGetLastError();
 }
 
+// Solid sites are static: the step kernels skip them, relying on BOTH population buffers holding their
+// values (the reference copies them every step, advection.d:83-85).  After a mask upload that follows the
+// populations, the sites that just became solid must therefore be copied into the other buffer once.
+__global__ void sync_solid_kernel(Geom g, const uint8_t *__restrict__ m, const double *__restrict__ src,
+                                  double *__restrict__ dst) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= g.nx) return;
+  const int y = blockIdx.y, zg = blockIdx.z;  // ghost planes included
+  const int64_t sxy = (int64_t)y * g.nx + x;
+  if (!m[(int64_t)zg * g.plane + sxy]) return;
+  for (int cq = 0; cq < g.ncomp * Q; cq++) {
+    const int64_t i = (int64_t)zg * g.fz + (int64_t)cq * g.plane + sxy;
+    dst[i] = src[i];
+  }
+}
+cudaError_t launch_sync_solid(const Geom &g, const uint8_t *m, const double *src, double *dst, cudaStream_t s) {
+  const unsigned bx = g.nx >= 128 ? 128 : ((g.nx + 31) / 32) * 32;
+  sync_solid_kernel<<<dim3((g.nx + bx - 1) / bx, g.ny, g.nz + 2), bx, 0, s>>>(g, m, src, dst);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_ghost_fill(const Geom &g, double *f, int narrays, cudaStream_t s) {
   dim3 grid((unsigned)((g.plane + 255) / 256), (unsigned)min(narrays, 65535));
   ghost_fill_kernel<<<grid, 256, 0, s>>>(g, f, narrays);

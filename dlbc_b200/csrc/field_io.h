@@ -26,6 +26,9 @@ cudaError_t launch_ghost_fill_mask(const Geom &g, uint8_t *m, cudaStream_t s);
 // neighbourhood solid flags (Fields::nb) of the physical planes from a mask whose ghost planes are valid
 cudaError_t launch_neighbour_bits(const Geom &g, const uint8_t *m, uint32_t *nb, cudaStream_t s);
 
+// copy the populations of solid sites (all components, ghost planes included) from src to dst
+cudaError_t launch_sync_solid(const Geom &g, const uint8_t *m, const double *src, double *dst, cudaStream_t s);
+
 // derived outputs into a dense, halo-free device array [nx][ny][nz][K]
 // kind 0 density(c1), 1 colour(c1 - c2), 2 raw velocity(c1), 3 copy of an SoA vector field [3][sites_g]
 cudaError_t launch_output(const Geom &g, int kind, const double *f, const uint8_t *mask, int c1, int c2, double *out,

@@ -11,7 +11,9 @@ struct StepLaunch {
   StepParams p;
   int eq, psi, sc, mask;
   cudaStream_t stream;
-  int *wave_sync;  // ticket + completion counters of the wave variant (wave_sync_ints() ints)
+  int *wave_sync;  // ticket + completion counters of the wave / TMA variants (wave_sync_ints() ints)
+  int wave_tyb;    // band height in rows, 0 = default (dlbc_cuda_set_option "wave_tyb")
+  int wave_la;     // lag of the fused items behind the psi items in slots, 0 = default ("wave_la")
 };
 
 // size of StepLaunch::wave_sync: 1 ticket + one completion counter per (band, ghost-inclusive plane, row of
@@ -37,12 +39,10 @@ typedef cudaError_t (*force_fn)(const StepLaunch &, int comp, double *out, int z
   cudaError_t launch_force_c##NC(const StepLaunch &, int, double *, int, int);       \
   cudaError_t launch_fused_exact_c##NC(const StepLaunch &, int, int);                \
   cudaError_t launch_fused_fast_c##NC(const StepLaunch &, int, int);                 \
-  cudaError_t launch_zmarch_exact_c##NC(const StepLaunch &, int, int);               \
-  cudaError_t launch_zmarch_fast_c##NC(const StepLaunch &, int, int);               \
-  cudaError_t launch_zpipe_exact_c##NC(const StepLaunch &, int, int);                \
-  cudaError_t launch_zpipe_fast_c##NC(const StepLaunch &, int, int);                 \
   cudaError_t launch_wave_exact_c##NC(const StepLaunch &, int, int);                 \
-  cudaError_t launch_wave_fast_c##NC(const StepLaunch &, int, int);
+  cudaError_t launch_wave_fast_c##NC(const StepLaunch &, int, int);                  \
+  cudaError_t launch_tma_exact_c##NC(const StepLaunch &, int, int);                  \
+  cudaError_t launch_tma_fast_c##NC(const StepLaunch &, int, int);
 DLBC_DECLARE_STEP(1)
 DLBC_DECLARE_STEP(2)
 DLBC_DECLARE_STEP(3)

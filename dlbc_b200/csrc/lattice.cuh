@@ -90,9 +90,6 @@ __device__ __forceinline__ double *psi_plane(double *p, const Geom &g, int zg, i
 // 64-bit index sum: shift, add, add-with-carry, LEA, LEA.HI.X -- 5-6 integer instructions per load, ~45 %
 // of the fused path's instruction stream (profiles/README.md).  All offsets a site update needs lie within
 // +-1 plane block of its own entry, hence 32 bits (see Geom).
-#ifndef DLBC_WIDE_STANDALONE
-#define DLBC_WIDE_STANDALONE 1
-#endif
 __device__ __forceinline__ const double *ptr_at(const double *base, int off) {
   const double *r;
   asm("mad.wide.s32 %0, %1, 8, %2;" : "=l"(r) : "r"(off), "l"(base));
@@ -110,11 +107,12 @@ __device__ __forceinline__ const uint8_t *ptr_at(const uint8_t *base, int off) {
 }
 
 // Loads through a ptr_at() address: the address-space inference is lost across the asm, so say .global
-// explicitly (a generic LD costs an extra address-space check).  ld_global is the ordinary coherent load
-// (psi written by other blocks of the same launch, step_wave.cuh), ld_global_nc the read-only path.
-__device__ __forceinline__ double ld_global(const double *a) {
+// explicitly (a generic LD costs an extra address-space check).  ld_global_cg is the L1-bypassing coherent
+// load for psi written by other blocks of the SAME launch (step_wave.cuh: always served by L2, where the
+// writers' release made it visible), ld_global_nc the read-only path.
+__device__ __forceinline__ double ld_global_cg(const double *a) {
   double v;
-  asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(a));
+  asm volatile("ld.global.cg.f64 %0, [%1];" : "=d"(v) : "l"(a) : "memory");
   return v;
 }
 __device__ __forceinline__ double ld_global_nc(const double *a) {

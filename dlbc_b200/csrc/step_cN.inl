@@ -4,9 +4,8 @@
 // reference order, exp) live in the EXACT unit only.
 #include "kernels.h"
 #include "step_two_pass.cuh"
-#include "step_zmarch.cuh"
-#include "step_zpipe.cuh"
 #include "step_wave.cuh"
+#include "step_tma.cuh"
 #include <cstdlib>
 
 namespace dlbc {
@@ -66,151 +65,28 @@ cudaError_t DLBC_MODE_NAME(launch_fused)(const StepLaunch &L, int z_begin, int z
   return cudaGetLastError();
 }
 
-// ---- z-marching single-pass variant (Shan-Chen only; C <= 2: 19 C doubles stay in registers) ----
-#if DLBC_NC <= 2
-template <int C, int EQ, int PSI, bool MASK, int TX, int TY, int MINB>
-static cudaError_t zmarch_launch(const StepLaunch &L, int z_begin, int z_count, int chunk) {
-  auto kern = zmarch_kernel<C, EQ, PSI, MASK, kExact, TX, TY, MINB>;
-  constexpr size_t smem = (size_t)(C * Q * TX * TY + 4 * C * (TX + 2) * (TY + 2)) * sizeof(double);
-  {
-    // per device (function attributes are not shared between the devices of one process)
-    static bool configured[64] = {};
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev < 0 || dev >= 64 || !configured[dev]) {
-      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e != cudaSuccess) return e;
-      if (dev >= 0 && dev < 64) configured[dev] = true;
-    }
-  }
-  ZMarch zm{z_begin, z_begin + z_count, chunk};
-  dim3 grid((L.g.nx + TX - 1) / TX, (L.g.ny + TY - 1) / TY, (z_count + chunk - 1) / chunk);
-  kern<<<grid, dim3(TX, TY), smem, L.stream>>>(L.g, L.f, L.p, zm);
-  return cudaGetLastError();
-}
-
-template <int C, int EQ, int PSI, bool MASK>
-static cudaError_t zmarch_tile(const StepLaunch &L, int z_begin, int z_count) {
-  // tuning knobs (measurement only; defaults are the measured best)
-  static const char *tile = std::getenv("DLBC_ZM_TILE");
-  static const char *ch = std::getenv("DLBC_ZM_CHUNK");
-  int chunk = ch ? std::atoi(ch) : 64;
-  if (chunk < 1) chunk = 64;
-  if (tile && tile[0] == '6' && tile[3] == '4') return zmarch_launch<C, EQ, PSI, MASK, 64, 4, 2>(L, z_begin, z_count, chunk);
-  if (tile && tile[0] == '3') return zmarch_launch<C, EQ, PSI, MASK, 32, 8, 2>(L, z_begin, z_count, chunk);
-  return zmarch_launch<C, EQ, PSI, MASK, 64, 8, 1>(L, z_begin, z_count, chunk);
-}
-
-template <int C, int EQ>
-static cudaError_t zmarch_eq(const StepLaunch &L, int z_begin, int z_count) {
-  if (L.psi == 0) return L.mask ? zmarch_tile<C, EQ, 0, true>(L, z_begin, z_count) : zmarch_tile<C, EQ, 0, false>(L, z_begin, z_count);
-  return L.mask ? zmarch_tile<C, EQ, 1, true>(L, z_begin, z_count) : zmarch_tile<C, EQ, 1, false>(L, z_begin, z_count);
-}
-#endif
-
-cudaError_t DLBC_MODE_NAME(launch_zmarch)(const StepLaunch &L, int z_begin, int z_count) {
-  if (z_count <= 0) return cudaSuccess;
-#if DLBC_NC <= 2
-  if (!L.sc) return cudaErrorNotSupported;
-  switch (L.eq) {
-    case 0: return zmarch_eq<DLBC_NC, 0>(L, z_begin, z_count);
-    case 1: return zmarch_eq<DLBC_NC, 1>(L, z_begin, z_count);
-    case 2: return zmarch_eq<DLBC_NC, 2>(L, z_begin, z_count);
-    default: return cudaErrorInvalidValue;
-  }
-#else
-  (void)z_begin;
-  return cudaErrorNotSupported;
-#endif
-}
-
-// ---- asynchronously pipelined z-march (step_zpipe.cuh) ----
-#if DLBC_NC <= 2
-template <int C, int EQ, int PSI, bool MASK, int TX, int TY>
-static cudaError_t zpipe_launch(const StepLaunch &L, int z_begin, int z_count, int chunk) {
-  auto kern = zpipe_kernel<C, EQ, PSI, MASK, kExact, TX, TY>;
-  constexpr int NT = TX * TY, NRIM = 2 * (TX + 2) + 2 * TY, RP = (TX + 2) * (TY + 2);
-  constexpr size_t smem = (size_t)(2 * C * Q * NT + C * Q * NRIM + 4 * C * RP) * sizeof(double);
-  static_assert(smem <= 227 * 1024, "zpipe tile does not fit in shared memory");
-  {
-    // per device (function attributes are not shared between the devices of one process)
-    static bool configured[64] = {};
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev < 0 || dev >= 64 || !configured[dev]) {
-      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e != cudaSuccess) return e;
-      if (dev >= 0 && dev < 64) configured[dev] = true;
-    }
-  }
-  ZMarch zm{z_begin, z_begin + z_count, chunk};
-  dim3 grid((L.g.nx + TX - 1) / TX, (L.g.ny + TY - 1) / TY, (z_count + chunk - 1) / chunk);
-  kern<<<grid, dim3(TX, TY), smem, L.stream>>>(L.g, L.f, L.p, zm);
-  return cudaGetLastError();
-}
-
-template <int C, int EQ, int PSI, bool MASK>
-static cudaError_t zpipe_tile(const StepLaunch &L, int z_begin, int z_count) {
-  static const char *tile = std::getenv("DLBC_ZP_TILE");
-  static const char *ch = std::getenv("DLBC_ZP_CHUNK");
-  int chunk = ch ? std::atoi(ch) : 128;
-  if (chunk < 1) chunk = 128;
-  if (tile && tile[0] == '6') return zpipe_launch<C, EQ, PSI, MASK, 64, 4>(L, z_begin, z_count, chunk);
-  return zpipe_launch<C, EQ, PSI, MASK, 32, 8>(L, z_begin, z_count, chunk);
-}
-
-template <int C, int EQ>
-static cudaError_t zpipe_eq(const StepLaunch &L, int z_begin, int z_count) {
-  if (L.psi == 0) return L.mask ? zpipe_tile<C, EQ, 0, true>(L, z_begin, z_count) : zpipe_tile<C, EQ, 0, false>(L, z_begin, z_count);
-  return L.mask ? zpipe_tile<C, EQ, 1, true>(L, z_begin, z_count) : zpipe_tile<C, EQ, 1, false>(L, z_begin, z_count);
-}
-#endif
-
-cudaError_t DLBC_MODE_NAME(launch_zpipe)(const StepLaunch &L, int z_begin, int z_count) {
-  if (z_count <= 0) return cudaSuccess;
-#if DLBC_NC <= 2
-  if (!L.sc) return cudaErrorNotSupported;
-  switch (L.eq) {
-    case 0: return zpipe_eq<DLBC_NC, 0>(L, z_begin, z_count);
-    case 1: return zpipe_eq<DLBC_NC, 1>(L, z_begin, z_count);
-    case 2: return zpipe_eq<DLBC_NC, 2>(L, z_begin, z_count);
-    default: return cudaErrorInvalidValue;
-  }
-#else
-  (void)z_begin;
-  return cudaErrorNotSupported;
-#endif
-}
-
-// ---- L2-ordered single launch (step_wave.cuh) ----
-template <int C, int EQ, int PSI, bool MASK, bool SPLIT>
-static cudaError_t wave_launch(const StepLaunch &L, int z_begin, int z_count) {
-  static const char *e_tyb = std::getenv("DLBC_WAVE_TYB");
-  static const char *e_la = std::getenv("DLBC_WAVE_LA");
-  static const char *e_pf = std::getenv("DLBC_WAVE_PF");      // prefetch distance in tickets (0 = off = default)
-  static const char *e_pfk = std::getenv("DLBC_WAVE_PFKEEP"); // 1 (default): prefetch with L2::evict_last
+// ---- L2-ordered single launch: schedule shared by the register path (step_wave.cuh) and the TMA path
+// (step_tma.cuh); `seg` = sites per item ----
+static cudaError_t wave_plan(const StepLaunch &L, int z_begin, int z_count, int seg, Wave &w) {
   const Geom &g = L.g;
   if (g.periodic_z_local && !(z_begin == 1 && z_count == g.nz)) return cudaErrorInvalidValue;
-  Wave w;
   w.z_begin = z_begin;
   w.z_end = z_begin + z_count;
   w.pre = g.periodic_z_local ? 1 : 0;
   w.pl = g.periodic_z_local ? 1 : (z_begin - 1 < 1 ? 1 : z_begin - 1);
   w.ph = g.periodic_z_local ? g.nz - 1 : (w.z_end > g.nz ? g.nz : w.z_end);
   // band-plane of ~16k sites (5 MB of populations at C = 2): measured best on 512^2 planes (profiles/README.md)
-  w.tyb = e_tyb ? std::atoi(e_tyb) : (int)(16384 / g.nx);
-  if (w.tyb < 8) w.tyb = 8;
+  w.tyb = L.wave_tyb > 0 ? L.wave_tyb : (int)(16384 / g.nx);
+  if (w.tyb < 8 && L.wave_tyb <= 0) w.tyb = 8;
   if (w.tyb > g.ny) w.tyb = g.ny;
-  w.xb = (g.nx + WAVE_SEG - 1) / WAVE_SEG;
+  w.seg = seg;
+  w.xb = (g.nx + seg - 1) / seg;
   // lag of F behind P: at least 2 slots (F(z) reads psi(z+1)); more when a band-plane is smaller than
-  // the ~80k sites the GPU keeps in flight, so that F blocks rarely have to wait.  With per-row completion
-  // counters (rowsync) an F item only waits for the 9 row segments it reads, and one slot less is best
-  // (512^2 planes, TYB = 32: LA 4 with rowsync 6.96 GLUPS, LA 5 without 6.81; profiles/README.md).
-  static const char *e_rs0 = std::getenv("DLBC_WAVE_ROWSYNC");
-  const int64_t lag_sites = (e_rs0 ? std::atoi(e_rs0) : 1) ? 65536 : 81920;
-  int la = e_la ? std::atoi(e_la) : (int)((lag_sites + (int64_t)w.tyb * g.nx - 1) / ((int64_t)w.tyb * g.nx));
+  // the ~64k sites the GPU keeps in flight, so that F items rarely have to wait (512^2 planes, TYB = 32:
+  // LA 4 measured best, profiles/README.md)
+  int la = L.wave_la > 0 ? L.wave_la : (int)((65536 + (int64_t)w.tyb * g.nx - 1) / ((int64_t)w.tyb * g.nx));
   if (la < 2) la = 2;
-  if (!e_la && la > 8) la = 8;
+  if (L.wave_la <= 0 && la > 8) la = 8;
   w.la = la;
   w.rp = (w.tyb + 2) * w.xb;
   w.rf = w.tyb * w.xb;
@@ -220,49 +96,41 @@ static cudaError_t wave_launch(const StepLaunch &L, int z_begin, int z_count) {
   w.nbands = (g.ny + w.tyb - 1) / w.tyb;
   w.sync = L.wave_sync;
   if (!w.sync) return cudaErrorInvalidValue;
-  const int64_t blocks = (int64_t)w.nbands * w.slots * (w.rp + w.rf);
-  if (blocks >= ((int64_t)1 << 31)) return cudaErrorInvalidConfiguration;
-  cudaError_t e = cudaMemsetAsync(w.sync, 0, wave_sync_ints(g, w.tyb) * sizeof(int), L.stream);
-  if (e != cudaSuccess) return e;
-  // persistent grid: as many blocks as can be resident (fewer when the launch is small)
-  static int resident = 0;
-  if (!resident) {
-    int dev = 0, sms = 0, per_sm = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wave_kernel<C, EQ, PSI, MASK, kExact, SPLIT>, WAVE_SEG * (SPLIT ? C : 1), 0);
-    resident = sms * (per_sm > 0 ? per_sm : 1);
-  }
-  const unsigned grid = (unsigned)(blocks < resident ? blocks : resident);
-  w.pf = e_pf ? std::atoi(e_pf) : 0;   // measured slower when on (profiles/r01_wave_experiments.md): L2 capacity, not latency, is the limit
-  w.pf_keep = e_pfk ? std::atoi(e_pfk) : 1;
-  static const char *e_batch = std::getenv("DLBC_WAVE_BATCH");
-  static const char *e_rs = std::getenv("DLBC_WAVE_ROWSYNC");
-  w.rowsync = e_rs ? std::atoi(e_rs) : 1;
-  w.batch = e_batch ? std::atoi(e_batch) : 1;  // with LA = 5: +2-4 % (LA = 4: -8 %), profiles/README.md
-  static const char *e_free = std::getenv("DLBC_WAVE_FREE");  // 1: barrier-free form (wave_free_kernel)
-  if (!SPLIT && (e_free ? std::atoi(e_free) != 0 : false)) {
-    wave_free_kernel<C, EQ, PSI, MASK, kExact><<<grid, WAVE_SEG, 0, L.stream>>>(g, L.f, L.p, w);
-    return cudaGetLastError();
-  }
-  wave_kernel<C, EQ, PSI, MASK, kExact, SPLIT><<<grid, dim3(WAVE_SEG, SPLIT ? C : 1), 0, L.stream>>>(g, L.f, L.p, w);
-  return cudaGetLastError();
+  const int64_t items = (int64_t)w.nbands * w.slots * (w.rp + w.rf);
+  if (items >= ((int64_t)1 << 31)) return cudaErrorInvalidConfiguration;
+  return cudaMemsetAsync(w.sync, 0, wave_sync_ints(g, w.tyb) * sizeof(int), L.stream);
 }
 
-template <int C, int EQ, bool SPLIT>
-static cudaError_t wave_psi(const StepLaunch &L, int z_begin, int z_count) {
-  if (L.psi == 0) return L.mask ? wave_launch<C, EQ, 0, true, SPLIT>(L, z_begin, z_count) : wave_launch<C, EQ, 0, false, SPLIT>(L, z_begin, z_count);
-  return L.mask ? wave_launch<C, EQ, 1, true, SPLIT>(L, z_begin, z_count) : wave_launch<C, EQ, 1, false, SPLIT>(L, z_begin, z_count);
+static int device_slot() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev >= 0 && dev < 64 ? dev : 0;
+}
+
+template <int C, int EQ, int PSI, bool MASK>
+static cudaError_t wave_launch(const StepLaunch &L, int z_begin, int z_count) {
+  Wave w;
+  cudaError_t e = wave_plan(L, z_begin, z_count, WAVE_SEG, w);
+  if (e != cudaSuccess) return e;
+  // persistent grid: as many blocks as can be resident (fewer when the launch is small); per device
+  static int resident[64] = {};
+  const int dev = device_slot();
+  if (!resident[dev]) {
+    int sms = 0, per_sm = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wave_kernel<C, EQ, PSI, MASK, kExact>, WAVE_SEG, 0);
+    resident[dev] = sms * (per_sm > 0 ? per_sm : 1);
+  }
+  const int64_t items = (int64_t)w.nbands * w.slots * (w.rp + w.rf);
+  const unsigned grid = (unsigned)(items < resident[dev] ? items : resident[dev]);
+  wave_kernel<C, EQ, PSI, MASK, kExact><<<grid, WAVE_SEG, 0, L.stream>>>(L.g, L.f, L.p, w);
+  return cudaGetLastError();
 }
 
 template <int C, int EQ>
 static cudaError_t wave_eq(const StepLaunch &L, int z_begin, int z_count) {
-  // DLBC_WAVE_SPLIT=1 selects the one-thread-per-(site, component) form (step_wave.cuh); measured
-  // slower than one thread per site (profiles/README.md), so it is off by default
-  static const char *e_split = std::getenv("DLBC_WAVE_SPLIT");
-  const bool split = C > 1 && (e_split ? std::atoi(e_split) != 0 : false);
-  if constexpr (C > 1) { if (split) return wave_psi<C, EQ, true>(L, z_begin, z_count); }
-  return wave_psi<C, EQ, false>(L, z_begin, z_count);
+  if (L.psi == 0) return L.mask ? wave_launch<C, EQ, 0, true>(L, z_begin, z_count) : wave_launch<C, EQ, 0, false>(L, z_begin, z_count);
+  return L.mask ? wave_launch<C, EQ, 1, true>(L, z_begin, z_count) : wave_launch<C, EQ, 1, false>(L, z_begin, z_count);
 }
 
 cudaError_t DLBC_MODE_NAME(launch_wave)(const StepLaunch &L, int z_begin, int z_count) {
@@ -272,6 +140,50 @@ cudaError_t DLBC_MODE_NAME(launch_wave)(const StepLaunch &L, int z_begin, int z_
     case 0: return wave_eq<DLBC_NC, 0>(L, z_begin, z_count);
     case 1: return wave_eq<DLBC_NC, 1>(L, z_begin, z_count);
     case 2: return wave_eq<DLBC_NC, 2>(L, z_begin, z_count);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+// ---- the same schedule fed by TMA bulk copies from a producer warp (step_tma.cuh) ----
+template <int C, int EQ, int PSI, bool MASK>
+static cudaError_t tma_launch(const StepLaunch &L, int z_begin, int z_count) {
+  // 16-byte copy granularity: x0, segment lengths and row starts must be even (multiples of 4 for the
+  // 4-byte neighbourhood words of the MASK instantiations)
+  if (L.g.nx % (MASK ? 4 : 2) != 0) return cudaErrorNotSupported;
+  Wave w;
+  cudaError_t e = wave_plan(L, z_begin, z_count, TMA_SEG, w);
+  if (e != cudaSuccess) return e;
+  auto kern = tma_kernel<C, EQ, PSI, MASK, kExact>;
+  constexpr int smem = tma_stages<C>() * tma_stage_bytes<C>();
+  static_assert(tma_stages<C>() >= 2, "a TMA stage does not fit twice into shared memory");
+  static int sms[64] = {};
+  const int dev = device_slot();
+  if (!sms[dev]) {
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
+  }
+  // one persistent CTA per SM; fewer when the launch holds fewer items than the CTAs could take at once
+  const int64_t items = (int64_t)w.nbands * w.slots * (w.rp + w.rf);
+  const int64_t want = (items + TMA_GROUPS - 1) / TMA_GROUPS;
+  const unsigned grid = (unsigned)(want < sms[dev] ? (want < 1 ? 1 : want) : sms[dev]);
+  kern<<<grid, TMA_THREADS, smem, L.stream>>>(L.g, L.f, L.p, w);
+  return cudaGetLastError();
+}
+
+template <int C, int EQ>
+static cudaError_t tma_eq(const StepLaunch &L, int z_begin, int z_count) {
+  if (L.psi == 0) return L.mask ? tma_launch<C, EQ, 0, true>(L, z_begin, z_count) : tma_launch<C, EQ, 0, false>(L, z_begin, z_count);
+  return L.mask ? tma_launch<C, EQ, 1, true>(L, z_begin, z_count) : tma_launch<C, EQ, 1, false>(L, z_begin, z_count);
+}
+
+cudaError_t DLBC_MODE_NAME(launch_tma)(const StepLaunch &L, int z_begin, int z_count) {
+  if (z_count <= 0) return cudaSuccess;
+  if (!L.sc) return cudaErrorNotSupported;
+  switch (L.eq) {
+    case 0: return tma_eq<DLBC_NC, 0>(L, z_begin, z_count);
+    case 1: return tma_eq<DLBC_NC, 1>(L, z_begin, z_count);
+    case 2: return tma_eq<DLBC_NC, 2>(L, z_begin, z_count);
     default: return cudaErrorInvalidValue;
   }
 }

@@ -87,8 +87,8 @@ __global__ void __launch_bounds__(128) psi_kernel(Geom g, Fields fl, int z_begin
 // ---- Shan-Chen force for all components of one site (force.d:238-309) -----------------------
 // Accumulation order per component f1 is the reference's: f2 outer, q = 1..18 inner, then the
 // wall term q = 0..18; prefactor = ((w_q * psi1) * psi2) * cc.
-// COHERENT: psi was written by other blocks of the SAME launch (step_wave.cuh): ordinary loads
-// instead of the read-only (ld.global.nc) path.
+// COHERENT: psi was written by other blocks of the SAME launch (step_wave.cuh): L1-bypassing loads
+// (ld.global.cg) instead of the read-only (ld.global.nc) path.
 template <int C, bool MASK, bool EXACT, bool COHERENT = false>
 __device__ __forceinline__ void shan_chen_force(const Geom &g, const Fields &fl, const StepParams &P, int zg,
                                                 const Nbr &n, uint32_t bits, const double (&psi1)[C], double (&F)[C][3]) {
@@ -102,14 +102,14 @@ __device__ __forceinline__ void shan_chen_force(const Geom &g, const Fields &fl,
       return __ldg(pp + f2 * cstride + d);
     });
   } else {
-    // psi was written by other blocks of this launch: coherent loads, 32-bit-offset addressing
+    // psi was written by other blocks of this launch: L2 loads (ld.global.cg), 32-bit-offset addressing
     const double *pp[C];
 #pragma unroll
     for (int c = 0; c < C; c++) pp[c] = psi_plane(fl.psi, g, zg, c) + n.sxy;
     sc_force<C, EXACT>(P, psi1, F, [&](int f2, int q) -> double {
       const int d = n.ox[1 + cx(q)] + n.oy[1 + cy(q)] + cz(q) * g.plane;
       if (MASK && ((bits >> q) & 1u)) return psi1[f2];
-      return ld_global(ptr_at(pp[f2], d));
+      return ld_global_cg(ptr_at(pp[f2], d));
     });
   }
 }
@@ -210,7 +210,10 @@ __device__ __forceinline__ void fused_site(const Geom &g, const Fields &fl, cons
   if (SC) {
     double psi1[C];
 #pragma unroll
-    for (int c = 0; c < C; c++) psi1[c] = psi_plane(fl.psi, g, zg, c)[n.sxy];
+    for (int c = 0; c < C; c++) {
+      const double *a = psi_plane(fl.psi, g, zg, c) + n.sxy;
+      psi1[c] = COHERENT ? ld_global_cg(a) : *a;
+    }
     shan_chen_force<C, MASK, EXACT, COHERENT>(g, fl, P, zg, n, bits, psi1, F);
     if (MASK && P.any_gwc) wall_force<C, POL != POL_DEFAULT>(g, fl, P, zg, n, bits, psi1, F);
   }

@@ -212,6 +212,17 @@ class Lattice:
         self._ck(self._l.dlbc_cuda_kernel_times(self._h, cap, names, ms, C.byref(n)))
         return [(names[i].decode(), ms[i]) for i in range(n.value)]
 
+    def set_option(self, name, value):
+        """Tuning knobs of the single-launch schedules ("wave_tyb", "wave_la"); results do not depend on them."""
+        self._ck(self._l.dlbc_cuda_set_option(self._h, name.encode(), int(value)))
+
+    @property
+    def kernel_variant(self):
+        """Name of the step kernel variant the next step runs (what "auto" resolved to)."""
+        v = C.c_int()
+        self._l.dlbc_cuda_kernel_variant(self._h, C.byref(v))
+        return {n: k for k, n in _lib.KERNEL.items()}[v.value]
+
     @property
     def launch_count(self):
         v = C.c_int64()

@@ -13,12 +13,12 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.environ.get("DLBC_CUDA_LIB") or os.path.join(HERE, "libdlbc_cuda.so")  # override: A/B runs of two builds
 MAXC = 4
 NCCL_ID_BYTES = 128
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 PSI = {"Linear": 0, "Exponential": 1}
 EQ = {"SecondOrder": 0, "ThirdOrder": 1, "BDist2": 2}
 ARITH = {"fast": 0, "exact": 1}
-KERNEL = {"auto": 0, "two_pass": 1, "zmarch": 2, "zpipe": 3, "wave": 4}
+KERNEL = {"auto": 0, "two_pass": 1, "wave": 2, "tma": 3}
 
 # every symbol include/dlbc_cuda.h declares (tests check that the library exports all of them)
 SYMBOLS = [
@@ -29,7 +29,8 @@ SYMBOLS = [
     "dlbc_cuda_step", "dlbc_cuda_sync", "dlbc_cuda_timestep", "dlbc_cuda_download_density",
     "dlbc_cuda_download_colour", "dlbc_cuda_download_velocity", "dlbc_cuda_download_force",
     "dlbc_cuda_total_mass", "dlbc_cuda_total_momentum", "dlbc_cuda_tables", "dlbc_cuda_launch_count",
-    "dlbc_cuda_timed_steps", "dlbc_cuda_kernel_times", "dlbc_cuda_device_bytes",
+    "dlbc_cuda_timed_steps", "dlbc_cuda_kernel_times", "dlbc_cuda_device_bytes", "dlbc_cuda_kernel_variant",
+    "dlbc_cuda_set_option",
 ]
 
 
@@ -94,6 +95,8 @@ def load():
     L.dlbc_cuda_timed_steps.argtypes = [vp, C.c_int, dp]
     L.dlbc_cuda_kernel_times.argtypes = [vp, C.c_int, C.POINTER(C.c_char_p), dp, C.POINTER(C.c_int)]
     L.dlbc_cuda_device_bytes.argtypes = [vp, i64p]
+    L.dlbc_cuda_kernel_variant.argtypes = [vp, C.POINTER(C.c_int)]
+    L.dlbc_cuda_set_option.argtypes = [vp, C.c_char_p, C.c_int64]
     for name in SYMBOLS:
         fn = getattr(L, name)
         if name not in ("dlbc_cuda_last_error", "dlbc_cuda_timestep"):

@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define DLBC_CUDA_ABI_VERSION 1
+#define DLBC_CUDA_ABI_VERSION 2
 #define DLBC_CUDA_MAX_COMPONENTS 4
 #define DLBC_CUDA_NCCL_ID_BYTES 128
 
@@ -51,15 +51,17 @@ enum {
   DLBC_ARITH_EXACT = 1  /* every fp64 operation as the reference performs it (IEEE divisions, same
                            order): bit-identical to the CPU restatement except for exp() */
 };
-/* step kernel variants (evidence for the design choice; results are identical) */
+/* step kernel variants (evidence for the design choice; results are identical bit for bit) */
 enum {
-  DLBC_KERNEL_AUTO = 0,
+  DLBC_KERNEL_AUTO = 0,       /* TMA where the lattice allows it (nx even; nx % 4 == 0 with solid sites) on one
+                                 rank and on thick z-slabs, else WAVE; TWO_PASS on thin slabs and without
+                                 Shan-Chen */
   DLBC_KERNEL_TWO_PASS = 1,   /* psi kernel + fused pull/force/collide kernel (psi via L1/L2) */
-  DLBC_KERNEL_ZMARCH = 2,     /* single pass: z-marching fused kernel, psi planes in shared memory */
-  DLBC_KERNEL_ZPIPE = 3,      /* single pass: z-march with the population loads as an asynchronous
-                                 cp.async shared-memory pipeline (loads of plane z+2 overlap plane z) */
-  DLBC_KERNEL_WAVE = 4        /* psi sites + fused sites in ONE launch, ticket-ordered band by band so
-                                 that the second gather of every population is an L2 hit */
+  DLBC_KERNEL_WAVE = 2,       /* psi sites + fused sites in ONE launch, ticket-ordered band by band so that the
+                                 second gather of every population is an L2 hit; per-thread register gathers */
+  DLBC_KERNEL_TMA = 3         /* the same schedule, warp-specialised: a producer warp stages population rows and
+                                 psi rows into shared memory with TMA bulk copies (cp.async.bulk + mbarrier),
+                                 consumer warps compute from shared memory */
 };
 
 /* Replaces: the module-level parameters the timestep reads -- lattice.gn (lattice.d:28),
@@ -154,6 +156,13 @@ int dlbc_cuda_launch_count(const dlbc_cuda_ctx *ctx, int64_t *count);
 int dlbc_cuda_timed_steps(dlbc_cuda_ctx *ctx, int nsteps, double *elapsed_ms);
 int dlbc_cuda_kernel_times(dlbc_cuda_ctx *ctx, int cap, const char **names, double *ms, int *n);
 int dlbc_cuda_device_bytes(const dlbc_cuda_ctx *ctx, int64_t *bytes);
+/* kernel_variant: the DLBC_KERNEL_* the next step will run (what AUTO resolved to).
+ * set_option: tuning knobs of the single-launch schedules, for measurements and for tests that must reach
+ * every scheduling regime on small lattices; 0 restores the default.  Names: "wave_tyb" (band height in
+ * rows), "wave_la" (lag of the fused items behind the psi items, in band-planes, >= 2).  Results do not
+ * depend on either.  Unknown names fail. */
+int dlbc_cuda_kernel_variant(const dlbc_cuda_ctx *ctx, int *variant);
+int dlbc_cuda_set_option(dlbc_cuda_ctx *ctx, const char *name, int64_t value);
 
 #ifdef __cplusplus
 }

@@ -33,3 +33,20 @@ def assert_bitexact(a, b, what=""):
 
 SC = dict(tau=[1.0, 1.0], gcc=[[0.0, 3.6], [3.6, 0.0]], psi_form="Exponential",
           eqdist_form="BDist2", enable_shan_chen=True)
+
+
+def random_case(gn, solid=0.0, seed=11, gwc=None, acc=(1e-5, -2e-5, 3e-5)):
+    """Two-component Shan-Chen case with random densities (and a random mask, solid sites initialised as
+    initEqDistWall does): (params, populations, mask)."""
+    from dlbc_b200 import init as I
+    from dlbc_b200.connectivity import d3q19
+    rng = np.random.default_rng(seed)
+    mask = (rng.random(gn) < solid).astype(np.int32) if solid > 0 else None
+    pops = []
+    for rho in (0.6, 0.12):
+        a = (rho + 0.05 * rng.random(gn))[..., None] * I.eq_dist_unity(d3q19, I.BDIST2)
+        pops.append(I.init_eq_dist_wall(a, mask) if mask is not None else a)
+    params = dict(gn=gn, components=2, global_acc=list(acc), **SC)
+    if gwc is not None:
+        params["gwc"] = list(gwc)
+    return params, pops, mask

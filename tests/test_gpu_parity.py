@@ -6,7 +6,7 @@ mode with no exp() on the path the populations must be bit-identical to the orac
 import numpy as np
 import pytest
 
-from helpers import SC, assert_bitexact, assert_close
+from helpers import SC, assert_bitexact, assert_close, random_case
 
 pytestmark = pytest.mark.gpu
 
@@ -17,7 +17,7 @@ from dlbc_b200.connectivity import d3q19  # noqa: E402
 from dlbc_b200.lattice import Lattice  # noqa: E402
 from oracle import oracle as O  # noqa: E402
 
-KERNELS = ["two_pass", "zmarch", "zpipe", "wave"]
+KERNELS = ["two_pass", "wave", "tma"]
 
 
 def make_pair(params, pops, mask, **gpu_kw):
@@ -331,3 +331,143 @@ def test_full_size_mass_and_linearity_256():
         G.step(10)
         shifted = G.get_populations_xrange(0, (100 + 48) % n, 2)
     assert_bitexact(shifted, np.roll(probe, (5, 7), axis=(1, 2)), "translation invariance")
+
+
+# ---- the single-launch schedules in every regime the 512^3 bench runs them in -----------------------
+# The wave / TMA kernels cut the lattice into y-bands of `wave_tyb` rows and x-segments of 128 / 64 sites and
+# let the fused items lag `wave_la` band-planes behind the psi items; band halo rows, the ragged last band,
+# the per-(band, plane, row) completion counters and the cross-band psi rewrites only exist when there is
+# more than one band, and the waits only bite when more items exist than the GPU holds at once.
+def _run_gpu(params, pops, mask, steps, options=None, **kw):
+    p = dict(params)
+    gn, nc = p.pop("gn"), p.pop("components")
+    with Lattice(gn, nc, **p, **kw) as G:
+        for k, v in (options or {}).items():
+            G.set_option(k, v)
+        if mask is not None:
+            G.set_mask(mask)
+        for c, a in enumerate(pops):
+            G.set_populations(c, a)
+        G.step(steps)
+        return [G.get_populations(c) for c in range(nc)], [G.density(c) for c in range(nc)]
+
+
+@pytest.mark.parametrize("solid", [0.0, 0.15])
+@pytest.mark.parametrize("arith", ["exact", "fast"])
+@pytest.mark.parametrize("gn", [(256, 192, 24), (200, 136, 20)])
+def test_single_launch_multi_band_default_geometry(gn, arith, solid):
+    """nx * ny > 16384 => several bands (256x192: 3 bands of 64 rows; 200x136: 81 + a ragged 55), 2-4
+    x-segments per row, lag 4 -- the geometry of the 512^3 bench.  wave and tma must equal two_pass BIT FOR
+    BIT (same site functions) and the oracle within tolerance."""
+    params, pops, mask = random_case(gn, solid)
+    steps = 8
+    ref_f, ref_d = _run_gpu(params, pops, mask, steps, arithmetic=arith, kernel="two_pass")
+    for kernel in ("wave", "tma"):
+        f, d = _run_gpu(params, pops, mask, steps, arithmetic=arith, kernel=kernel)
+        for c in range(2):
+            assert_bitexact(f[c], ref_f[c], f"{kernel} vs two_pass {gn} {arith} solid={solid}: populations {c}")
+            assert_bitexact(d[c], ref_d[c], f"{kernel} vs two_pass {gn}: density {c}")
+    p = dict(params); g = p.pop("gn"); nc = p.pop("components")
+    R = O.OracleLattice(g, nc, **p)
+    if mask is not None:
+        R.set_mask(mask)
+    for c, a in enumerate(pops):
+        R.set_populations(c, a)
+    R.exchange_halo()
+    R.step(steps)
+    for c in range(2):
+        assert_close(ref_f[c], R.get_populations(c), what=f"{gn} {arith} solid={solid} vs oracle: populations {c}")
+
+
+@pytest.mark.parametrize("kernel", ["wave", "tma"])
+@pytest.mark.parametrize("tyb,la", [(8, 2), (8, 4), (5, 3), (1, 2)])
+@pytest.mark.parametrize("gn,solid", [((132, 20, 12), 0.0), ((64, 44, 10), 0.2), ((260, 19, 6), 0.0), ((72, 9, 3), 0.1)])
+def test_single_launch_forced_bands(gn, solid, tyb, la, kernel):
+    """Small lattices forced into >= 3 bands with the minimum lag (dlbc_cuda_set_option): ragged last band,
+    rows that wrap around y inside a band halo, 1-3 x-segments, nz as small as 3; EXACT arithmetic,
+    bit-identical to two_pass and within tolerance of the oracle."""
+    params, pops, mask = random_case(gn, solid, seed=5, gwc=[-0.03, 0.04] if solid else None)
+    steps = 6
+    ref_f, _ = _run_gpu(params, pops, mask, steps, arithmetic="exact", kernel="two_pass")
+    f, _ = _run_gpu(params, pops, mask, steps, options=dict(wave_tyb=tyb, wave_la=la), arithmetic="exact", kernel=kernel)
+    for c in range(2):
+        assert_bitexact(f[c], ref_f[c], f"{kernel} tyb={tyb} la={la} {gn}: populations {c}")
+    G, R = make_pair(params, pops, mask, arithmetic="exact", kernel=kernel)
+    G.set_option("wave_tyb", tyb)
+    G.set_option("wave_la", la)
+    G.step(steps)
+    R.step(steps)
+    compare_state(G, R, 2, f"{kernel} tyb={tyb} la={la} {gn} vs oracle", steps=steps)
+    G.close()
+
+
+def test_spinodal_twin_128():
+    """config 3 twin at 128^3, 10 steps against the oracle with the default (auto) kernel and FAST
+    arithmetic -- what the bench runs -- in 8 bands of 16 rows (the default band at nx = 128 is 128 rows)."""
+    params, pops, _ = cases.spinodal(128)
+    G, R = make_pair(params, pops, None)
+    assert G.kernel_variant == "tma"
+    G.set_option("wave_tyb", 16)
+    G.step(10)
+    R.step(10)
+    compare_state(G, R, 2, "spinodal 128^3 t10", steps=10)
+    G.close()
+
+
+def test_porous_twin_64():
+    """config 4 twin at 64^3 (30 % solid from Mt19937(1234)), default kernel, 4 bands, 10 steps."""
+    params, pops, mask = cases.porous(64)
+    G, R = make_pair(params, pops, mask)
+    G.set_option("wave_tyb", 16)
+    m0 = [G.total_mass(c) for c in range(2)]
+    G.step(10)
+    R.step(10)
+    compare_state(G, R, 2, "porous 64^3 t10", steps=10)
+    for c in range(2):
+        assert abs(G.total_mass(c) - m0[c]) / m0[c] < 10 * 1e-14
+    G.close()
+
+
+def test_auto_falls_back_on_odd_nx_and_explicit_tma_fails():
+    params, pops, mask = random_case((33, 6, 4))
+    p = dict(params); gn = p.pop("gn"); nc = p.pop("components")
+    with Lattice(gn, nc, **p) as G:
+        assert G.kernel_variant == "wave"   # 16-byte TMA rows need an even nx
+    with Lattice(gn, nc, **p, kernel="tma") as G:
+        for c, a in enumerate(pops):
+            G.set_populations(c, a)
+        with pytest.raises(dlib.DlbcCudaError, match="even nx"):
+            G.step(1)
+    with Lattice((34, 6, 4), nc, **p) as G:
+        assert G.kernel_variant == "tma"
+        G.set_mask((np.arange(34 * 6 * 4).reshape(34, 6, 4) % 7 == 0).astype(np.int32))
+        assert G.kernel_variant == "wave"   # 4-byte neighbourhood words: nx % 4 == 0 once solids exist
+    with Lattice(gn, nc, **p) as G:
+        with pytest.raises(dlib.DlbcCudaError):
+            G.set_option("no_such_option", 1)
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_mask_uploaded_after_populations_and_steps(kernel):
+    """upload order must not matter: solid sites hold their values in BOTH population buffers
+    (advection.d:83-85 copies them every step), also when the mask arrives after some steps."""
+    params, pops, mask = random_case((24, 12, 10), solid=0.2, seed=9)
+    p = dict(params); gn = p.pop("gn"); nc = p.pop("components")
+    with Lattice(gn, nc, **p, arithmetic="exact", kernel=kernel) as G:
+        for c, a in enumerate(pops):
+            G.set_populations(c, a)
+        G.step(3)                      # no mask yet: all sites fluid
+        mid = [G.get_populations(c) for c in range(nc)]
+        G.set_mask(mask)
+        G.step(3)                      # an odd number: the "other" buffer is the current one now
+        got = [G.get_populations(c) for c in range(nc)]
+    R = O.OracleLattice(gn, nc, **p)
+    for c in range(nc):
+        R.set_populations(c, mid[c])
+    R.set_mask(mask)
+    R.exchange_halo()
+    R.step(3)
+    solid = mask == 1
+    for c in range(nc):
+        assert_bitexact(got[c][solid], mid[c][solid], f"{kernel}: solid sites keep their populations")
+        assert_close(got[c], R.get_populations(c), what=f"{kernel}: mask after populations, populations {c}")

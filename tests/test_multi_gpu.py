@@ -8,7 +8,7 @@ import threading
 import numpy as np
 import pytest
 
-from helpers import assert_bitexact, assert_close
+from helpers import assert_bitexact, assert_close, random_case
 
 pytestmark = pytest.mark.gpu
 
@@ -25,7 +25,7 @@ def _ngpu():
         return 0
 
 
-def run_slabs(params, pops, mask, nranks, steps, **kw):
+def run_slabs(params, pops, mask, nranks, steps, options=None, **kw):
     """Run `steps` timesteps on `nranks` GPUs; returns the gathered global populations, masses."""
     p = dict(params)
     gn, nc = p.pop("gn"), p.pop("components")
@@ -37,6 +37,8 @@ def run_slabs(params, pops, mask, nranks, steps, **kw):
         try:
             z0, z1 = slab_range(gn[2], r, nranks)
             with Lattice(gn, nc, **p, device=r, rank=r, nranks=nranks, nccl_id=nccl_id, **kw) as G:
+                for k, v in (options or {}).items():
+                    G.set_option(k, v)
                 if mask is not None:
                     G.set_mask(np.ascontiguousarray(mask[:, :, z0:z1]))
                 for c, a in enumerate(pops):
@@ -61,7 +63,7 @@ def run_slabs(params, pops, mask, nranks, steps, **kw):
     return f, d, out[0][2]
 
 
-@pytest.mark.parametrize("kernel", ["two_pass", "zpipe", "wave"])
+@pytest.mark.parametrize("kernel", ["two_pass", "wave", "tma"])
 @pytest.mark.parametrize("nranks", [2, 4, 8])
 def test_decomposition_invariance_spinodal(kernel, nranks):
     if _ngpu() < nranks:
@@ -75,7 +77,7 @@ def test_decomposition_invariance_spinodal(kernel, nranks):
         assert abs(mg[c] - m1[c]) <= 1e-13 * abs(m1[c])
 
 
-@pytest.mark.parametrize("kernel", ["two_pass", "wave"])
+@pytest.mark.parametrize("kernel", ["two_pass", "wave", "tma"])
 def test_decomposition_invariance_porous_wall_term(kernel):
     if _ngpu() < 2:
         pytest.skip("needs 2 GPUs")
@@ -84,6 +86,24 @@ def test_decomposition_invariance_porous_wall_term(kernel):
     fg, _, _ = run_slabs(params, pops, mask, 2, 5, arithmetic="exact", kernel=kernel)
     for c in range(2):
         assert_bitexact(fg[c], f1[c], f"{kernel}: porous populations {c}")
+
+
+@pytest.mark.parametrize("kernel", ["wave", "tma"])
+@pytest.mark.parametrize("nranks", [2, 4])
+def test_decomposition_invariance_multi_band_slabs(kernel, nranks):
+    """The single-launch schedules on z-slabs in the multi-band regime (4 bands of 8 rows + a ragged one,
+    minimum lag, 3 x-segments for the TMA kernel), with a mask: 1 GPU, G slabs and the two-kernel schedule
+    must agree bit for bit."""
+    if _ngpu() < nranks:
+        pytest.skip(f"needs {nranks} GPUs")
+    params, pops, mask = random_case((136, 36, 8 * nranks), solid=0.1, seed=21)
+    opts = dict(wave_tyb=8, wave_la=2)
+    f1, _, _ = run_slabs(params, pops, mask, 1, 6, arithmetic="exact", kernel="two_pass")
+    fs, _, _ = run_slabs(params, pops, mask, 1, 6, options=opts, arithmetic="exact", kernel=kernel)
+    fg, _, _ = run_slabs(params, pops, mask, nranks, 6, options=opts, arithmetic="exact", kernel=kernel)
+    for c in range(2):
+        assert_bitexact(fs[c], f1[c], f"{kernel} 1 GPU vs two_pass: populations {c}")
+        assert_bitexact(fg[c], f1[c], f"{kernel} x{nranks} vs two_pass on 1 GPU: populations {c}")
 
 
 def test_two_slabs_match_oracle():
