@@ -299,6 +299,9 @@ def run_ours(args, rank, world, local_rank):
         params["global_acc"] = [0.0, 0.0, 1e-5]
     G = Lattice(gn, ncomp, **params, arithmetic=args.arith, kernel=args.kernel, device=local_rank,
                 rank=rank, nranks=world, nccl_id=nccl_id)
+    for name, v in (("wave_tyb", args.wave_tyb), ("wave_la", args.wave_la)):
+        if v:
+            G.set_option(name, v)
     gl = G.n
     sites_local = gl[0] * gl[1] * gl[2]
     sites_total = sites_local * world
@@ -467,6 +470,8 @@ def main():
                     help="porous: BASELINE configs[3] (mask-heavy path), device-resident timing only")
     ap.add_argument("--arith", default="fast", choices=["fast", "exact"])
     ap.add_argument("--kernel", default="auto", choices=["auto", "two_pass", "wave", "tma"])
+    ap.add_argument("--wave-tyb", type=int, default=0, help="band height of the single-launch kernels (0: default)")
+    ap.add_argument("--wave-la", type=int, default=0, help="lag of the fused items behind the psi items (0: default)")
     ap.add_argument("--cpu-sample", type=int, default=128)
     ap.add_argument("--cpu-steps", type=int, default=20)
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -263,7 +263,8 @@ struct KernelTimer {
 
 // The TMA variant moves rows in 16-byte units: nx must be even, and a multiple of 4 once solid sites exist
 // (4-byte neighbourhood words).  AUTO falls back to the register path; an explicit request fails in step().
-bool tma_ok(const dlbc_cuda_ctx *ctx) { return ctx->g.nx % (ctx->has_solid ? 4 : 2) == 0; }
+// C = 4 does not fit enough stages next to the consumer groups (step_tma.cuh: stages must outnumber the groups).
+bool tma_ok(const dlbc_cuda_ctx *ctx) { return ctx->g.nx % (ctx->has_solid ? 4 : 2) == 0 && ctx->cfg.ncomp <= 3; }
 int effective_variant(const dlbc_cuda_ctx *ctx) {
   if (ctx->variant == DLBC_KERNEL_TMA && ctx->variant_auto && !tma_ok(ctx)) return DLBC_KERNEL_WAVE;
   return ctx->variant;
@@ -547,7 +548,7 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
   // two-kernel schedule wins back below ~128 planes
   ctx->variant_auto = cfg->kernel_variant == DLBC_KERNEL_AUTO;
   ctx->variant = !ctx->variant_auto ? cfg->kernel_variant
-                 : (cfg->nranks == 1 || ctx->g.nz >= 160 ? DLBC_KERNEL_TMA : DLBC_KERNEL_TWO_PASS);
+                 : (cfg->nranks == 1 || ctx->g.nz >= 160 ? DLBC_KERNEL_WAVE : DLBC_KERNEL_TWO_PASS);
   if (!cfg->enable_shan_chen) ctx->variant = DLBC_KERNEL_TWO_PASS;  // nothing to order: one fused kernel per step
 
   CKC(cudaStreamCreateWithFlags(&ctx->compute, cudaStreamNonBlocking));

@@ -150,6 +150,9 @@ static cudaError_t tma_launch(const StepLaunch &L, int z_begin, int z_count) {
   // 16-byte copy granularity: x0, segment lengths and row starts must be even (multiples of 4 for the
   // 4-byte neighbourhood words of the MASK instantiations)
   if (L.g.nx % (MASK ? 4 : 2) != 0) return cudaErrorNotSupported;
+  // a consumer group may wait for the full barrier of item n only once item n - NS has been staged: with at
+  // least as many groups as stages, item NS would be claimed while the barrier is still in its first phase
+  if (tma_stages<C>() <= TMA_GROUPS) return cudaErrorNotSupported;
   Wave w;
   cudaError_t e = wave_plan(L, z_begin, z_count, TMA_SEG, w);
   if (e != cudaSuccess) return e;

@@ -270,6 +270,8 @@ def test_ragged_sizes(gn):
         pops.append(I.init_eq_dist_wall(a, mask))
     params = dict(gn=gn, components=2, global_acc=[1e-5, 0, 0], **SC)
     for kernel in KERNELS:
+        if kernel == "tma" and gn[0] % 4:
+            continue  # 16-byte copy granularity (test_auto_falls_back_on_odd_nx_and_explicit_tma_fails)
         G, R = make_pair(params, pops, mask, kernel=kernel)
         G.step(6)
         R.step(6)
