@@ -44,8 +44,8 @@ def _stale(target, sources):
     return any(os.path.getmtime(s) > t for s in sources)
 
 
-def _compile(src, flags, force, verbose):
-    obj = os.path.join(OBJ, src.replace(".cu", ".o"))
+def _compile(src, flags, force, verbose, objdir=None):
+    obj = os.path.join(objdir or OBJ, src.replace(".cu", ".o"))
     if not force and not _stale(obj, [os.path.join(CSRC, src)] + _deps()):
         return obj
     cmd = [NVCC] + ARCH + COMMON + flags + ["-Xptxas", "-v" if verbose else "-warn-spills", "-c",
@@ -59,18 +59,23 @@ def _compile(src, flags, force, verbose):
     return obj
 
 
-def build(force=False, jobs=None, verbose=False):
-    os.makedirs(OBJ, exist_ok=True)
+def build(force=False, jobs=None, verbose=False, out=None, defines=()):
+    """out / defines: an A/B build (scripts/gpu_ab.sh) -- its own object directory, -D flags, another .so."""
+    so = os.path.abspath(out) if out else SO
+    objdir = OBJ if not out else os.path.join(CSRC, "build_" + os.path.splitext(os.path.basename(so))[0])
+    os.makedirs(objdir, exist_ok=True)
+    os.makedirs(os.path.dirname(so), exist_ok=True)
     jobs = jobs or min(10, os.cpu_count() or 4)
     us = units()
+    dflags = ["-D" + d for d in defines]
     with ThreadPoolExecutor(jobs) as ex:
-        objs = list(ex.map(lambda u: _compile(u[0], u[1], force, verbose), us))
-    if force or _stale(SO, objs):
-        cmd = [NVCC] + ARCH + ["-shared", "-o", SO] + objs + ["-lcudart_static", "-ldl", "-lpthread", "-lrt"]
+        objs = list(ex.map(lambda u: _compile(u[0], u[1] + dflags, force, verbose, objdir), us))
+    if force or _stale(so, objs):
+        cmd = [NVCC] + ARCH + ["-shared", "-o", so] + objs + ["-lcudart_static", "-ldl", "-lpthread", "-lrt"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
-    return SO
+    return so
 
 
 if __name__ == "__main__":
@@ -78,5 +83,7 @@ if __name__ == "__main__":
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--jobs", type=int, default=None)
     ap.add_argument("--verbose", action="store_true", help="keep ptxas -v output next to the objects")
+    ap.add_argument("--out", default=None, help="A/B build: path of the .so (objects go to csrc/build_<name>)")
+    ap.add_argument("--define", action="append", default=[], help="-D macro for an A/B build, e.g. DLBC_TMA_CWARPS=8")
     a = ap.parse_args()
-    print(build(a.force, a.jobs, a.verbose))
+    print(build(a.force, a.jobs, a.verbose, a.out, a.define))

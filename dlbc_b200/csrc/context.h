@@ -42,6 +42,9 @@ struct dlbc_cuda_ctx {
   cudaEvent_t ev_stage[2] = {nullptr, nullptr};  // compute: the conversion kernel has consumed half i
   double *partial = nullptr;          // device, reduction partials
   int *flags = nullptr;               // device, [2]: bad mask value seen, solid count
+  // TMA variant: tensor maps of both population buffers (boxes of 3 slots / 1 slot) and of psi (step_tma.cuh)
+  CUtensorMap tma_pop3[2], tma_pop1[2], tma_psi;
+  bool tma_maps = false;
   int *wave_sync[3] = {nullptr, nullptr, nullptr};  // wave variant: ticket + counters (interior, lower, upper boundary launch)
 
   // multi-rank

@@ -121,6 +121,9 @@ StepLaunch make_launch(dlbc_cuda_ctx *ctx, cudaStream_t s) {
   L.wave_sync = ctx->wave_sync[0];
   L.wave_tyb = ctx->opt_wave_tyb;
   L.wave_la = ctx->opt_wave_la;
+  L.tma_pop3 = ctx->tma_maps ? &ctx->tma_pop3[ctx->cur] : nullptr;  // maps of f_old
+  L.tma_pop1 = ctx->tma_maps ? &ctx->tma_pop1[ctx->cur] : nullptr;
+  L.tma_psi = ctx->tma_maps ? &ctx->tma_psi : nullptr;
   return L;
 }
 
@@ -261,10 +264,45 @@ struct KernelTimer {
   }
 };
 
-// The TMA variant moves rows in 16-byte units: nx must be even, and a multiple of 4 once solid sites exist
-// (4-byte neighbourhood words).  AUTO falls back to the register path; an explicit request fails in step().
-// C = 4 does not fit enough stages next to the consumer groups (step_tma.cuh: stages must outnumber the groups).
-bool tma_ok(const dlbc_cuda_ctx *ctx) { return ctx->g.nx % (ctx->has_solid ? 4 : 2) == 0 && ctx->cfg.ncomp <= 3; }
+// Tensor maps of the TMA variant (step_tma.cuh): populations as the 5-D tensor f[zg][c][slot][y][x] with boxes
+// [TMA_SEG + 4, 1, 3 or 1 slots, C, 1], psi as the 4-D tensor psi[c][zg][y][x] with box [TMA_SEG + 4, 1, 3, C].
+// Out-of-range columns are zero-filled.  Needs an even nx (16-byte strides); C <= 2 (stage count, step_tma.cuh).
+typedef CUresult (*tensor_map_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                         const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                         CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+bool make_tma_maps(dlbc_cuda_ctx *ctx) {
+  const Geom &g = ctx->g;
+  const int C = ctx->cfg.ncomp;
+  if (g.nx % 2 != 0 || C > 2) return false;
+  static tensor_map_encode_fn encode = nullptr;
+  if (!encode) {
+    cudaDriverEntryPointQueryResult q;
+    void *fn = nullptr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn) return false;
+    encode = (tensor_map_encode_fn)fn;
+  }
+  const cuuint32_t ones[5] = {1, 1, 1, 1, 1};
+  for (int b = 0; b < 2; b++) {
+    const cuuint64_t dim[5] = {(cuuint64_t)g.nx, (cuuint64_t)g.ny, (cuuint64_t)Q, (cuuint64_t)C, (cuuint64_t)(g.nz + 2)};
+    const cuuint64_t str[4] = {(cuuint64_t)g.nx * 8, (cuuint64_t)g.plane * 8, (cuuint64_t)g.fc * 8, (cuuint64_t)g.fz * 8};
+    for (int k = 0; k < 2; k++) {
+      const cuuint32_t box[5] = {(cuuint32_t)(TMA_SEG + 4), 1, k == 0 ? 3u : 1u, (cuuint32_t)C, 1};
+      CUtensorMap *m = k == 0 ? &ctx->tma_pop3[b] : &ctx->tma_pop1[b];
+      if (encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 5, ctx->f[b], dim, str, box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                 CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return false;
+    }
+  }
+  const cuuint64_t dim[4] = {(cuuint64_t)g.nx, (cuuint64_t)g.ny, (cuuint64_t)(g.nz + 2), (cuuint64_t)C};
+  const cuuint64_t str[3] = {(cuuint64_t)g.nx * 8, (cuuint64_t)g.plane * 8, (cuuint64_t)g.sites_g * 8};
+  const cuuint32_t box[4] = {(cuuint32_t)(TMA_SEG + 4), 1, 3, (cuuint32_t)C};
+  return encode(&ctx->tma_psi, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, ctx->psi, dim, str, box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// The TMA variant has no mask path and needs the tensor maps (even nx, C <= 2).  AUTO falls back to the register
+// path; an explicit request fails in step().
+bool tma_ok(const dlbc_cuda_ctx *ctx) { return ctx->tma_maps && !ctx->has_solid; }
 int effective_variant(const dlbc_cuda_ctx *ctx) {
   if (ctx->variant == DLBC_KERNEL_TMA && ctx->variant_auto && !tma_ok(ctx)) return DLBC_KERNEL_WAVE;
   return ctx->variant;
@@ -581,6 +619,7 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
     ctx->device_bytes += (int64_t)(wave_sync_alloc_ints(g) * sizeof(int));
   }
   ctx->device_bytes += (int64_t)(2 * fbytes + sbytes + g.sites_g + (4 * REDUCE_BLOCKS + 4) * sizeof(double) + 8);
+  ctx->tma_maps = make_tma_maps(ctx);
   CKC(cudaMemsetAsync(ctx->f[0], 0, fbytes, ctx->compute));
   CKC(cudaMemsetAsync(ctx->f[1], 0, fbytes, ctx->compute));
   CKC(cudaMemsetAsync(ctx->psi, 0, sbytes, ctx->compute));
@@ -762,7 +801,7 @@ int dlbc_cuda_step(dlbc_cuda_ctx *ctx, int nsteps) {
   ARG(nsteps >= 0, "step: negative step count");
   if (nsteps == 0) return 0;
   ARG(effective_variant(ctx) != DLBC_KERNEL_TMA || tma_ok(ctx),
-      "step: the TMA kernel needs an even nx (a multiple of 4 with solid sites); use AUTO or WAVE");
+      "step: the TMA kernel needs an even nx, at most 2 components and no solid sites; use AUTO or WAVE");
   TRY(ensure_ghosts(ctx));
   if (ctx->cfg.nranks > 1 && ctx->timestep == 0) CK(cudaEventRecord(ctx->ev_ghost_f, ctx->compute));
   for (int i = 0; i < nsteps; i++) TRY(step_once(ctx, nullptr));
@@ -913,7 +952,7 @@ int dlbc_cuda_set_option(dlbc_cuda_ctx *ctx, const char *name, int64_t value) {
 int dlbc_cuda_timed_steps(dlbc_cuda_ctx *ctx, int nsteps, double *elapsed_ms) {
   TRY(check_ctx(ctx));
   ARG(nsteps >= 0 && elapsed_ms, "timed_steps: bad argument");
-  ARG(effective_variant(ctx) != DLBC_KERNEL_TMA || tma_ok(ctx), "timed_steps: the TMA kernel needs an even nx");
+  ARG(effective_variant(ctx) != DLBC_KERNEL_TMA || tma_ok(ctx), "timed_steps: the TMA kernel needs an even nx, at most 2 components and no solid sites");
   TRY(ensure_ghosts(ctx));
   if (ctx->cfg.nranks > 1 && ctx->timestep == 0) CK(cudaEventRecord(ctx->ev_ghost_f, ctx->compute));
   TRY(join_comm(ctx));

@@ -197,7 +197,7 @@ __device__ __forceinline__ void load_site(const double *__restrict__ f, const Ge
                                           double (&v)[Q]) {
   const double *__restrict__ p = f_plane(f, g, zg, c) + sxy;
 #pragma unroll
-  for (int q = 0; q < Q; q++) v[q] = p[q * g.plane];
+  for (int q = 0; q < Q; q++) v[q] = p[qslot(q) * g.plane];
 }
 
 template <int KIND>

@@ -1,5 +1,6 @@
 // kernels.h -- host-callable launchers of the step kernels (implemented in step_c*.cu).
 #pragma once
+#include <cuda.h>  // CUtensorMap (type only: the driver entry point is resolved at run time)
 #include <cuda_runtime.h>
 #include "lattice.cuh"
 
@@ -14,7 +15,12 @@ struct StepLaunch {
   int *wave_sync;  // ticket + completion counters of the wave / TMA variants (wave_sync_ints() ints)
   int wave_tyb;    // band height in rows, 0 = default (dlbc_cuda_set_option "wave_tyb")
   int wave_la;     // lag of the fused items behind the psi items in slots, 0 = default ("wave_la")
+  // TMA variant: tensor maps of f_old (3-slot and 1-slot boxes) and of psi, built by the host layer
+  // (dlbc_cuda.cu make_tma_maps); nullptr when the lattice has no TMA path
+  const CUtensorMap *tma_pop3, *tma_pop1, *tma_psi;
 };
+
+constexpr int TMA_SEG = 64;  // sites per item of the TMA variant == x extent of its boxes minus the 4 pad columns
 
 // size of StepLaunch::wave_sync: 1 ticket + one completion counter per (band, ghost-inclusive plane, row of
 // the band incl. its two halo rows); allocated for the worst case (band height 1: 3 rows per band)

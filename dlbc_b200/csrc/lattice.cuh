@@ -6,7 +6,8 @@
 namespace dlbc {
 
 // Device layout (DESIGN.md "Data layout in HBM"), plane-major structure of arrays:
-//   populations  f[zg][c][q][y][x]   fp64, x fastest; zg in [0, nz+2): planes 0 and nz+1 are ghosts
+//   populations  f[zg][c][s][y][x]   fp64, x fastest; zg in [0, nz+2): planes 0 and nz+1 are ghosts;
+//                                    s = qslot(q), the storage slot of direction q (lb_site.cuh)
 //   psi          psi[c][zg][y][x]    fp64, same ghosts
 //   mask         m[zg][y][x]         uint8 (0 = None, 1 = Solid), same ghosts
 // One z-plane of ALL C*19 population arrays is one contiguous block of C*19*nx*ny doubles, so
@@ -38,7 +39,7 @@ struct Fields {
 };
 
 __host__ __device__ __forceinline__ int64_t f_index(const Geom &g, int c, int q, int zg, int64_t sxy) {
-  return (int64_t)zg * g.fz + (int64_t)c * g.fc + (int64_t)q * g.plane + sxy;
+  return (int64_t)zg * g.fz + (int64_t)c * g.fc + (int64_t)qslot_rt(q) * g.plane + sxy;
 }
 
 __device__ __forceinline__ int wrap_inc(int i, int n) { return i + 1 == n ? 0 : i + 1; }
@@ -165,9 +166,9 @@ __device__ __forceinline__ void pull19(const double *__restrict__ ps, const uint
 #pragma unroll
     for (int q = 0; q < Q; q++) {
       const int d = n.ox[1 - cx(q)] + n.oy[1 - cy(q)];  // in-plane offset to the upstream site p - c_q
-      int src = q * g.plane - cz(q) * g.fz + d;
+      int src = qslot(q) * g.plane - cz(q) * g.fz + d;
       if (MASK && q > 0) {
-        if (ms[d - cz(q) * g.plane]) src = bounce(q) * g.plane;
+        if (ms[d - cz(q) * g.plane]) src = qslot(bounce(q)) * g.plane;
       }
       f[q] = load_pop<POL>(ps + src, pol);
     }
@@ -176,9 +177,9 @@ __device__ __forceinline__ void pull19(const double *__restrict__ ps, const uint
 #pragma unroll
     for (int q = 0; q < Q; q++) {
       const int d = n.ox[1 - cx(q)] + n.oy[1 - cy(q)];
-      int src = q * g.plane - cz(q) * g.fz + d;
+      int src = qslot(q) * g.plane - cz(q) * g.fz + d;
       if (MASK && q > 0) {
-        if (ld_mask(ptr_at(ms, d - cz(q) * g.plane))) src = bounce(q) * g.plane;
+        if (ld_mask(ptr_at(ms, d - cz(q) * g.plane))) src = qslot(bounce(q)) * g.plane;
       }
       f[q] = load_pop<POL>(ptr_at(ps, src), pol);
     }
@@ -196,8 +197,8 @@ __device__ __forceinline__ void pull19_bits(const double *__restrict__ ps, uint3
 #pragma unroll
   for (int q = 0; q < Q; q++) {
     const int d = n.ox[1 - cx(q)] + n.oy[1 - cy(q)];
-    int src = q * g.plane - cz(q) * g.fz + d;
-    if (q > 0 && ((bits >> bounce(q)) & 1u)) src = bounce(q) * g.plane;
+    int src = qslot(q) * g.plane - cz(q) * g.fz + d;
+    if (q > 0 && ((bits >> bounce(q)) & 1u)) src = qslot(bounce(q)) * g.plane;
     if (POL == POL_DEFAULT) f[q] = load_pop<POL>(ps + src, pol);
     else f[q] = load_pop<POL>(ptr_at(ps, src), pol);
   }

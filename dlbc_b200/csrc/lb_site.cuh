@@ -32,6 +32,27 @@ __host__ __device__ constexpr int bounce(int q) {
   constexpr int t[Q] = {0, 2, 1, 4, 3, 6, 5, 14, 13, 16, 15, 18, 17, 8, 7, 10, 9, 12, 11};
   return t[q];
 }
+// Storage slot of direction q inside a component's block of 19 planes (DEVICE layout only; the C ABI speaks
+// the reference's q order, field_io.cu converts).  Directions that stream from the same neighbouring ROW --
+// equal (c_y, c_z) -- sit in consecutive slots, so that one TMA box of 3 planes fetches all three
+// (step_tma.cuh: 9 copies per item instead of 19 per component):
+//   slots 0-2: q 0 1 2 (0,0) | 3-5: q 3 7 8 (+y) | 6-8: q 4 13 14 (-y) | 9-11: q 5 11 17 (+z) | 12-14: q 6 12 18 (-z)
+//   15: q 9 (+y+z) | 16: q 10 (-y+z) | 17: q 15 (+y-z) | 18: q 16 (-y-z)
+__host__ __device__ constexpr int qslot(int q) {
+  constexpr int t[Q] = {0, 1, 2, 3, 6, 9, 12, 4, 5, 15, 16, 10, 13, 7, 8, 17, 18, 11, 14};
+  return t[q];
+}
+// the same for a run-time q (no table in local memory): 5-bit codes
+__host__ __device__ constexpr unsigned long long qslot_pack(int lo, int hi) {
+  unsigned long long m = 0;
+  for (int q = lo; q < hi; q++) m |= (unsigned long long)qslot(q) << (5 * (q - lo));
+  return m;
+}
+__host__ __device__ inline int qslot_rt(int q) {
+  constexpr unsigned long long a = qslot_pack(0, 12), b = qslot_pack(12, Q);
+  return (int)(((q < 12 ? a >> (5 * q) : b >> (5 * (q - 12)))) & 31u);
+}
+
 // lb/connectivity.d:253-257
 __host__ __device__ constexpr double weight(int q) {
   return q == 0 ? 1.0 / 3.0 : (q < 7 ? 1.0 / 18.0 : 1.0 / 36.0);

@@ -79,8 +79,10 @@ static cudaError_t wave_plan(const StepLaunch &L, int z_begin, int z_count, int 
   w.tyb = L.wave_tyb > 0 ? L.wave_tyb : (int)(16384 / g.nx);
   if (w.tyb < 8 && L.wave_tyb <= 0) w.tyb = 8;
   if (w.tyb > g.ny) w.tyb = g.ny;
-  w.seg = seg;
-  w.xb = (g.nx + seg - 1) / seg;
+  w.seg = seg > 0 ? seg : g.nx;  // seg == 0: one ticket per row, cut into TMA_SEG-site items by the TMA producers
+  w.xb = (g.nx + w.seg - 1) / w.seg;
+  w.nsub = seg > 0 ? 1 : (g.nx + TMA_SEG - 1) / TMA_SEG;
+  w.alt = seg > 0 ? 0 : 1;
   // lag of F behind P: at least 2 slots (F(z) reads psi(z+1)); more when a band-plane is smaller than
   // the ~64k sites the GPU keeps in flight, so that F items rarely have to wait (512^2 planes, TYB = 32:
   // LA 4 measured best, profiles/README.md)
@@ -144,40 +146,38 @@ cudaError_t DLBC_MODE_NAME(launch_wave)(const StepLaunch &L, int z_begin, int z_
   }
 }
 
-// ---- the same schedule fed by TMA bulk copies from a producer warp (step_tma.cuh) ----
-template <int C, int EQ, int PSI, bool MASK>
+// ---- the same schedule fed by tensor-map TMA copies from producer warps (step_tma.cuh) ----
+template <int C, int EQ, int PSI>
 static cudaError_t tma_launch(const StepLaunch &L, int z_begin, int z_count) {
-  // 16-byte copy granularity: x0, segment lengths and row starts must be even (multiples of 4 for the
-  // 4-byte neighbourhood words of the MASK instantiations)
-  if (L.g.nx % (MASK ? 4 : 2) != 0) return cudaErrorNotSupported;
-  // a consumer group may wait for the full barrier of item n only once item n - NS has been staged: with at
-  // least as many groups as stages, item NS would be claimed while the barrier is still in its first phase
-  if (tma_stages<C>() <= TMA_GROUPS) return cudaErrorNotSupported;
-  Wave w;
-  cudaError_t e = wave_plan(L, z_begin, z_count, TMA_SEG, w);
-  if (e != cudaSuccess) return e;
-  auto kern = tma_kernel<C, EQ, PSI, MASK, kExact>;
-  constexpr int smem = tma_stages<C>() * tma_stage_bytes<C>();
-  static_assert(tma_stages<C>() >= 2, "a TMA stage does not fit twice into shared memory");
-  static int sms[64] = {};
-  const int dev = device_slot();
-  if (!sms[dev]) {
-    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if constexpr (C > 2) {
+    return cudaErrorNotSupported;  // C >= 3: the stages of a 57-double site do not fit (and neither do its registers)
+  } else {
+    // no mask path; 16-byte box starts and strides need an even nx; the host layer builds the tensor maps
+    if (L.mask || L.g.nx % 2 != 0 || !L.tma_pop3 || !L.tma_pop1 || !L.tma_psi) return cudaErrorNotSupported;
+    Wave w;
+    cudaError_t e = wave_plan(L, z_begin, z_count, 0, w);
     if (e != cudaSuccess) return e;
-    cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
+    auto kern = tma_kernel<C, EQ, PSI, kExact>;
+    constexpr int smem = tma_smem_bytes<C>();
+    static int sms[64] = {};
+    const int dev = device_slot();
+    if (!sms[dev]) {
+      e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      if (e != cudaSuccess) return e;
+      cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
+    }
+    // one persistent CTA per SM; fewer when the launch holds fewer items than the CTAs could take at once
+    const int64_t items = (int64_t)w.nbands * w.slots * (w.rp + w.rf) * w.nsub;
+    const int64_t want = (items + 3) / 4;
+    const unsigned grid = (unsigned)(want < sms[dev] ? (want < 1 ? 1 : want) : sms[dev]);
+    kern<<<grid, TMA_THREADS, smem, L.stream>>>(L.g, L.f, L.p, w, *L.tma_pop3, *L.tma_pop1, *L.tma_psi);
+    return cudaGetLastError();
   }
-  // one persistent CTA per SM; fewer when the launch holds fewer items than the CTAs could take at once
-  const int64_t items = (int64_t)w.nbands * w.slots * (w.rp + w.rf);
-  const int64_t want = (items + TMA_GROUPS - 1) / TMA_GROUPS;
-  const unsigned grid = (unsigned)(want < sms[dev] ? (want < 1 ? 1 : want) : sms[dev]);
-  kern<<<grid, TMA_THREADS, smem, L.stream>>>(L.g, L.f, L.p, w);
-  return cudaGetLastError();
 }
 
 template <int C, int EQ>
 static cudaError_t tma_eq(const StepLaunch &L, int z_begin, int z_count) {
-  if (L.psi == 0) return L.mask ? tma_launch<C, EQ, 0, true>(L, z_begin, z_count) : tma_launch<C, EQ, 0, false>(L, z_begin, z_count);
-  return L.mask ? tma_launch<C, EQ, 1, true>(L, z_begin, z_count) : tma_launch<C, EQ, 1, false>(L, z_begin, z_count);
+  return L.psi == 0 ? tma_launch<C, EQ, 0>(L, z_begin, z_count) : tma_launch<C, EQ, 1>(L, z_begin, z_count);
 }
 
 cudaError_t DLBC_MODE_NAME(launch_tma)(const StepLaunch &L, int z_begin, int z_count) {

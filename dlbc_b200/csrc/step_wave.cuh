@@ -39,7 +39,9 @@ struct Wave {
   int tyb;             // band height (rows)
   int la;              // F lags P by `la` slots
   int seg;             // sites per item (row segment length)
-  int xb;              // items per row
+  int xb;              // tickets per row
+  int alt;             // P and F tickets of a slot alternate row by row (TMA variant)
+  int nsub;            // items per ticket (TMA variant: a ticket is a whole row cut into TMA_SEG-site items; else 1)
   int rp, rf;          // P / F items per slot: (tyb + 2) * xb, tyb * xb
   int slots;           // slots per band
   int nbands;
@@ -62,13 +64,23 @@ __device__ __forceinline__ WaveItem wave_decode(const Geom &g, const Wave &w, in
   const int band = t / per_band;
   const int r = t - band * per_band;
   const int k = r / per_slot;
-  const int j = r - k * per_slot;
+  int j = r - k * per_slot;
   const int yb = band * w.tyb;
   const int tb = min(w.tyb, g.ny - yb);  // rows of this (possibly ragged) band
   WaveItem it;
   it.kind = 0;
   it.cnt = 1 + band * (g.nz + 2) * (w.tyb + 2);
-  if (j < w.rp) {
+  // order within a slot: all P items, then all F items; or (w.alt, one ticket per row) P row r, F row r, ...
+  // so that both kinds of work are always in flight (nothing in a slot depends on anything else in it)
+  int jp = j, jf = j - w.rp;
+  bool is_p = j < w.rp;
+  if (w.alt) {
+    is_p = j >= 2 * w.rf || (j & 1) == 0;
+    jp = j >= 2 * w.rf ? j - w.rf : j >> 1;
+    jf = j >> 1;
+  }
+  if (is_p) {
+    j = jp;
     int p = -1;
     if (k == 0) { if (w.pre) p = g.nz; }
     else if (w.pl + (k - 1) <= w.ph) p = w.pl + (k - 1);
@@ -80,7 +92,6 @@ __device__ __forceinline__ WaveItem wave_decode(const Geom &g, const Wave &w, in
     }
   } else if (k > 0) {
     const int zf = w.pl + (k - 1) - w.la;  // `la` slots behind the P item of the same plane (pl < z_begin on slabs)
-    const int jf = j - w.rp;
     const int row = jf / w.xb, xblk = jf - row * w.xb;
     if (zf >= w.z_begin && zf < w.z_end && row < tb) {
       it.kind = 2; it.zg = zf; it.y = yb + row; it.x0 = xblk * w.seg; it.row = row;
@@ -106,6 +117,23 @@ __device__ __forceinline__ const int *wave_wait_counter(const Geom &g, const Wav
 // The psi loads themselves bypass L1 (ld.global.cg in shan_chen_force / fused_site, COHERENT mode): a
 // 32-byte sector can straddle a row boundary, so a line another item pulled into L1 may hold last step's
 // values of a row that was not complete then.
+// Watchdog of every spin wait of the single-launch kernels: a protocol error must end the launch with an error
+// (trap -> "unspecified launch failure" at the next synchronisation) instead of hanging the GPU.
+constexpr long long WAVE_WATCHDOG_CYCLES = 20000000000ll;  // ~10 s at 2 GHz; a legitimate wait is microseconds
+struct Watchdog {
+  long long t0 = 0;
+  __device__ __forceinline__ void tick() {
+    const long long now = clock64();
+    if (t0 == 0) t0 = now;
+    else if (now - t0 > WAVE_WATCHDOG_CYCLES) __trap();
+  }
+};
+// wait until *p >= target (relaxed polls; the caller adds the acquire fence)
+__device__ __forceinline__ int ld_poll(const int *p);
+__device__ __forceinline__ void wave_poll_until(const int *p, int target, unsigned ns) {
+  Watchdog wd;
+  while (ld_poll(p) < target) { __nanosleep(ns); wd.tick(); }
+}
 __device__ __forceinline__ int ld_poll(const int *p) {
   int v;
   asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
@@ -146,7 +174,7 @@ wave_kernel(Geom g, Fields fl, StepParams P, Wave w) {
     } else if (wi.kind == 2) {
       if (threadIdx.x < 9) {
         const int *c = wave_wait_counter(g, w, wi, threadIdx.x);
-        if (c) while (ld_poll(c) < w.xb) __nanosleep(32);
+        if (c) wave_poll_until(c, w.xb * w.nsub, 32);
         wave_acquire();
       }
       __syncthreads();

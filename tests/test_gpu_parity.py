@@ -20,6 +20,12 @@ from oracle import oracle as O  # noqa: E402
 KERNELS = ["two_pass", "wave", "tma"]
 
 
+def tma_scope(kernel, gn, mask=None, nc=2):
+    """The TMA variant covers lattices without solid sites, an even nx and at most two components
+    (step_tma.cuh); everything else is the register path's (AUTO picks it, an explicit request is an error)."""
+    return kernel != "tma" or (gn[0] % 2 == 0 and nc <= 2 and (mask is None or not np.any(mask)))
+
+
 def make_pair(params, pops, mask, **gpu_kw):
     """The same case on the GPU and in the oracle."""
     p = dict(params)
@@ -240,6 +246,8 @@ def test_spinodal_twin(arith, kernel):
 def test_porous_twin(gwc, kernel):
     """config 4 twin (24x20x28, 30 % random solid): bounce-back + SC next to walls + wall adhesion."""
     params, pops, mask = cases.porous((24, 20, 28), gwc=gwc)
+    if not tma_scope(kernel, (24, 20, 28), mask):
+        pytest.skip("the TMA variant has no mask path")
     G, R = make_pair(params, pops, mask, kernel=kernel)
     assert_bitexact(G.get_mask(), mask, "mask round trip")
     m0 = [G.total_mass(c) for c in range(2)]
@@ -270,8 +278,8 @@ def test_ragged_sizes(gn):
         pops.append(I.init_eq_dist_wall(a, mask))
     params = dict(gn=gn, components=2, global_acc=[1e-5, 0, 0], **SC)
     for kernel in KERNELS:
-        if kernel == "tma" and gn[0] % 4:
-            continue  # 16-byte copy granularity (test_auto_falls_back_on_odd_nx_and_explicit_tma_fails)
+        if not tma_scope(kernel, gn, mask):
+            continue
         G, R = make_pair(params, pops, mask, kernel=kernel)
         G.step(6)
         R.step(6)
@@ -365,6 +373,8 @@ def test_single_launch_multi_band_default_geometry(gn, arith, solid):
     steps = 8
     ref_f, ref_d = _run_gpu(params, pops, mask, steps, arithmetic=arith, kernel="two_pass")
     for kernel in ("wave", "tma"):
+        if not tma_scope(kernel, gn, mask):
+            continue
         f, d = _run_gpu(params, pops, mask, steps, arithmetic=arith, kernel=kernel)
         for c in range(2):
             assert_bitexact(f[c], ref_f[c], f"{kernel} vs two_pass {gn} {arith} solid={solid}: populations {c}")
@@ -383,12 +393,15 @@ def test_single_launch_multi_band_default_geometry(gn, arith, solid):
 
 @pytest.mark.parametrize("kernel", ["wave", "tma"])
 @pytest.mark.parametrize("tyb,la", [(8, 2), (8, 4), (5, 3), (1, 2)])
-@pytest.mark.parametrize("gn,solid", [((132, 20, 12), 0.0), ((64, 44, 10), 0.2), ((260, 19, 6), 0.0), ((72, 9, 3), 0.1)])
+@pytest.mark.parametrize("gn,solid", [((132, 20, 12), 0.0), ((64, 44, 10), 0.2), ((260, 19, 6), 0.0), ((72, 9, 3), 0.1),
+                                      ((64, 44, 10), 0.0), ((70, 9, 3), 0.0)])
 def test_single_launch_forced_bands(gn, solid, tyb, la, kernel):
     """Small lattices forced into >= 3 bands with the minimum lag (dlbc_cuda_set_option): ragged last band,
     rows that wrap around y inside a band halo, 1-3 x-segments, nz as small as 3; EXACT arithmetic,
     bit-identical to two_pass and within tolerance of the oracle."""
     params, pops, mask = random_case(gn, solid, seed=5, gwc=[-0.03, 0.04] if solid else None)
+    if not tma_scope(kernel, gn, mask):
+        pytest.skip("the TMA variant has no mask path")
     steps = 6
     ref_f, _ = _run_gpu(params, pops, mask, steps, arithmetic="exact", kernel="two_pass")
     f, _ = _run_gpu(params, pops, mask, steps, options=dict(wave_tyb=tyb, wave_la=la), arithmetic="exact", kernel=kernel)
@@ -403,12 +416,13 @@ def test_single_launch_forced_bands(gn, solid, tyb, la, kernel):
     G.close()
 
 
-def test_spinodal_twin_128():
-    """config 3 twin at 128^3, 10 steps against the oracle with the default (auto) kernel and FAST
-    arithmetic -- what the bench runs -- in 8 bands of 16 rows (the default band at nx = 128 is 128 rows)."""
+@pytest.mark.parametrize("kernel", ["auto", "wave", "tma"])
+def test_spinodal_twin_128(kernel):
+    """config 3 twin at 128^3, 10 steps against the oracle with FAST arithmetic -- what the bench
+    runs -- in 8 bands of 16 rows (the default band at nx = 128 is 128 rows)."""
     params, pops, _ = cases.spinodal(128)
-    G, R = make_pair(params, pops, None)
-    assert G.kernel_variant == "tma"
+    G, R = make_pair(params, pops, None, kernel=kernel)
+    assert G.kernel_variant in ("wave", "tma")
     G.set_option("wave_tyb", 16)
     G.step(10)
     R.step(10)
@@ -434,25 +448,49 @@ def test_auto_falls_back_on_odd_nx_and_explicit_tma_fails():
     params, pops, mask = random_case((33, 6, 4))
     p = dict(params); gn = p.pop("gn"); nc = p.pop("components")
     with Lattice(gn, nc, **p) as G:
-        assert G.kernel_variant == "wave"   # 16-byte TMA rows need an even nx
+        assert G.kernel_variant == "wave"   # 16-byte TMA box starts / strides need an even nx
     with Lattice(gn, nc, **p, kernel="tma") as G:
         for c, a in enumerate(pops):
             G.set_populations(c, a)
         with pytest.raises(dlib.DlbcCudaError, match="even nx"):
             G.step(1)
-    with Lattice((34, 6, 4), nc, **p) as G:
+    with Lattice((34, 6, 4), nc, **p, kernel="tma") as G:
         assert G.kernel_variant == "tma"
         G.set_mask((np.arange(34 * 6 * 4).reshape(34, 6, 4) % 7 == 0).astype(np.int32))
-        assert G.kernel_variant == "wave"   # 4-byte neighbourhood words: nx % 4 == 0 once solids exist
+        with pytest.raises(dlib.DlbcCudaError, match="no solid sites"):
+            G.step(1)                       # no mask path in the TMA variant
+    with Lattice((34, 6, 4), nc, **p) as G:
+        G.set_mask((np.arange(34 * 6 * 4).reshape(34, 6, 4) % 7 == 0).astype(np.int32))
+        assert G.kernel_variant == "wave"   # AUTO: solid sites => register path
     with Lattice(gn, nc, **p) as G:
         with pytest.raises(dlib.DlbcCudaError):
             G.set_option("no_such_option", 1)
+
+
+@pytest.mark.parametrize("gn", [(6, 5, 3), (34, 2, 2), (130, 3, 2), (2, 2, 2), (16, 16, 40), (64, 3, 3), (66, 4, 5), (126, 7, 4)])
+@pytest.mark.parametrize("arith", ["exact", "fast"])
+def test_tma_ragged_sizes(gn, arith):
+    """the TMA variant on extents that are not multiples of its 64-site items, down to 2 (every neighbour wraps:
+    both edge patches in one item), without a mask; bit-identical to two_pass, within tolerance of the oracle."""
+    params, pops, _ = random_case(gn, 0.0, seed=13)
+    ref_f, ref_d = _run_gpu(params, pops, None, 6, arithmetic=arith, kernel="two_pass")
+    f, d = _run_gpu(params, pops, None, 6, arithmetic=arith, kernel="tma")
+    for c in range(2):
+        assert_bitexact(f[c], ref_f[c], f"tma vs two_pass {gn} {arith}: populations {c}")
+        assert_bitexact(d[c], ref_d[c], f"tma vs two_pass {gn} {arith}: density {c}")
+    G, R = make_pair(params, pops, None, arithmetic=arith, kernel="tma")
+    G.step(6)
+    R.step(6)
+    compare_state(G, R, 2, f"tma ragged {gn} {arith} vs oracle", steps=6)
+    G.close()
 
 
 @pytest.mark.parametrize("kernel", KERNELS)
 def test_mask_uploaded_after_populations_and_steps(kernel):
     """upload order must not matter: solid sites hold their values in BOTH population buffers
     (advection.d:83-85 copies them every step), also when the mask arrives after some steps."""
+    if kernel == "tma":
+        pytest.skip("the TMA variant has no mask path")
     params, pops, mask = random_case((24, 12, 10), solid=0.2, seed=9)
     p = dict(params); gn = p.pop("gn"); nc = p.pop("components")
     with Lattice(gn, nc, **p, arithmetic="exact", kernel=kernel) as G:
