@@ -67,7 +67,7 @@ cudaError_t DLBC_MODE_NAME(launch_fused)(const StepLaunch &L, int z_begin, int z
 
 // ---- L2-ordered single launch: schedule shared by the register path (step_wave.cuh) and the TMA path
 // (step_tma.cuh); `seg` = sites per item ----
-static cudaError_t wave_plan(const StepLaunch &L, int z_begin, int z_count, int seg, Wave &w) {
+static cudaError_t wave_plan(const StepLaunch &L, int z_begin, int z_count, int seg, int alt, Wave &w) {
   const Geom &g = L.g;
   if (g.periodic_z_local && !(z_begin == 1 && z_count == g.nz)) return cudaErrorInvalidValue;
   w.z_begin = z_begin;
@@ -79,10 +79,10 @@ static cudaError_t wave_plan(const StepLaunch &L, int z_begin, int z_count, int 
   w.tyb = L.wave_tyb > 0 ? L.wave_tyb : (int)(16384 / g.nx);
   if (w.tyb < 8 && L.wave_tyb <= 0) w.tyb = 8;
   if (w.tyb > g.ny) w.tyb = g.ny;
-  w.seg = seg > 0 ? seg : g.nx;  // seg == 0: one ticket per row, cut into TMA_SEG-site items by the TMA producers
+  w.seg = seg;
   w.xb = (g.nx + w.seg - 1) / w.seg;
-  w.nsub = seg > 0 ? 1 : (g.nx + TMA_SEG - 1) / TMA_SEG;
-  w.alt = seg > 0 ? 0 : 1;
+  w.nsub = 1;
+  w.alt = alt;
   // lag of F behind P: at least 2 slots (F(z) reads psi(z+1)); more when a band-plane is smaller than
   // the ~64k sites the GPU keeps in flight, so that F items rarely have to wait (512^2 planes, TYB = 32:
   // LA 4 measured best, profiles/README.md)
@@ -112,7 +112,7 @@ static int device_slot() {
 template <int C, int EQ, int PSI, bool MASK>
 static cudaError_t wave_launch(const StepLaunch &L, int z_begin, int z_count) {
   Wave w;
-  cudaError_t e = wave_plan(L, z_begin, z_count, WAVE_SEG, w);
+  cudaError_t e = wave_plan(L, z_begin, z_count, WAVE_SEG, 0, w);
   if (e != cudaSuccess) return e;
   // persistent grid: as many blocks as can be resident (fewer when the launch is small); per device
   static int resident[64] = {};
@@ -155,7 +155,7 @@ static cudaError_t tma_launch(const StepLaunch &L, int z_begin, int z_count) {
     // no mask path; 16-byte box starts and strides need an even nx; the host layer builds the tensor maps
     if (L.mask || L.g.nx % 2 != 0 || !L.tma_pop3 || !L.tma_pop1 || !L.tma_psi) return cudaErrorNotSupported;
     Wave w;
-    cudaError_t e = wave_plan(L, z_begin, z_count, 0, w);
+    cudaError_t e = wave_plan(L, z_begin, z_count, TMA_SEG, 1, w);
     if (e != cudaSuccess) return e;
     auto kern = tma_kernel<C, EQ, PSI, kExact>;
     constexpr int smem = tma_smem_bytes<C>();
@@ -167,8 +167,8 @@ static cudaError_t tma_launch(const StepLaunch &L, int z_begin, int z_count) {
       cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
     }
     // one persistent CTA per SM; fewer when the launch holds fewer items than the CTAs could take at once
-    const int64_t items = (int64_t)w.nbands * w.slots * (w.rp + w.rf) * w.nsub;
-    const int64_t want = (items + 3) / 4;
+    const int64_t items = (int64_t)w.nbands * w.slots * (w.rp + w.rf);
+    const int64_t want = (items + 2 * TMA_LANES - 1) / (2 * TMA_LANES);
     const unsigned grid = (unsigned)(want < sms[dev] ? (want < 1 ? 1 : want) : sms[dev]);
     kern<<<grid, TMA_THREADS, smem, L.stream>>>(L.g, L.f, L.p, w, *L.tma_pop3, *L.tma_pop1, *L.tma_psi);
     return cudaGetLastError();

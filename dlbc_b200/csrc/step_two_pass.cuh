@@ -50,13 +50,7 @@ __device__ __forceinline__ void psi_site(const Geom &g, const Fields &fl, int x,
   const Nbr n = make_nbr(g, x, y);
   const uint8_t *ms = mask_plane(fl.mask, g, zg) + n.sxy;
   const uint32_t bits = site_bits<MASK, POL>(g, fl, zg, n);
-  if (MASK && (bits & 1u)) {
-    // psi of solid sites is never read (force.d:273 uses the own-site psi); a value is stored all the same so
-    // that the warp writes whole 32-byte sectors (no fill reads, see fused_site)
-#pragma unroll
-    for (int c = 0; c < C; c++) psi_plane(fl.psi, g, zg, c)[n.sxy] = 0.0;
-    return;
-  }
+  if (MASK && (bits & 1u)) return;  // psi of solid sites is never read (force.d:273 uses the own-site psi)
   const double *ps = f_plane(fl.f_old, g, zg, 0) + n.sxy;
   double v[C];
   if (BATCH) {
@@ -200,24 +194,12 @@ __device__ __forceinline__ void fused_site(const Geom &g, const Fields &fl, cons
   const Nbr n = make_nbr(g, x, y);
   const uint8_t *ms = mask_plane(fl.mask, g, zg) + n.sxy;
   const uint32_t bits = site_bits<MASK, POL>(g, fl, zg, n);
-  // Solid sites: advection copies them (advection.d:83-85) and they never collide.  Both population buffers
-  // hold their (static) values since upload, so the copy changes nothing -- but it is made anyway: a 32-byte
-  // DRAM sector holds four sites, and a sector that the fluid sites of a warp write only in part has to be
-  // FILLED from DRAM by the L2 before it can be written back (porous 512^3, 30 % solid: 23.2 GB read per
-  // 33.5 M sites against 12.1 GB without a mask, profiles/README.md).  Whole sectors are written blind.
-  if (MASK && (bits & 1u)) {
-    const double *src = f_plane(fl.f_old, g, zg, 0) + n.sxy;
-    double *dst = f_plane(fl.f_new, g, zg, 0) + n.sxy;
-#pragma unroll
-    for (int c = 0; c < C; c++) {
-      double v[Q];
-#pragma unroll
-      for (int q = 0; q < Q; q++) v[q] = ld_global_nc(ptr_at(src, c * g.fc + q * g.plane));
-#pragma unroll
-      for (int q = 0; q < Q; q++) *ptr_at(dst, c * g.fc + q * g.plane) = v[q];
-    }
-    return;
-  }
+  // Solid sites: advection copies them (advection.d:83-85) and they never collide; both population buffers hold
+  // their (static) values since upload, so there is nothing to do.  (The fluid sites of a warp then write 32-byte
+  // sectors only in part, which the L2 has to fill from DRAM first: 23.2 GB read per 33.5 M sites on the porous
+  // workload against 12.1 GB without a mask.  Writing the solid sites' values back as well removes the fill
+  // reads but costs 38 loads + 38 stores per solid thread: measured 10 % SLOWER, profiles/README.md.)
+  if (MASK && (bits & 1u)) return;
 
   double f[C][Q], rho[C], m[C][3], F[C][3];
   const double *ps = f_plane(fl.f_old, g, zg, 0) + n.sxy;
