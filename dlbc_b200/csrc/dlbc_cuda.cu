@@ -445,6 +445,83 @@ int download_field(dlbc_cuda_ctx *ctx, int kind, int c1, int c2, const double *v
   return release_stage(ctx);
 }
 
+// After the physical planes of ctx->mask have been written (upload or generation on the device): ghost planes,
+// the "any solid site anywhere" decision, the neighbourhood bits, and the solid sites' values in both buffers.
+int finish_mask(dlbc_cuda_ctx *ctx, int solid) {
+  const Geom &g = ctx->g;
+  if (ctx->cfg.nranks == 1) {
+    CK(launch_ghost_fill_mask(g, ctx->mask, ctx->compute));
+    ctx->launches++;
+  } else {
+    TRY(exchange_planes<uint8_t>(ctx, scalar_xfer(ctx, ctx->mask, 1), ncclUint8, ctx->compute));
+    // "has_solid" also has to cover solids in the neighbours' boundary planes (our ghosts): count globally
+    int *dflag = ctx->flags + 1;
+    CK(cudaMemcpyAsync(dflag, &solid, sizeof(int), cudaMemcpyHostToDevice, ctx->compute));
+    NK(nccl_api().AllReduce(dflag, dflag, 1, ncclInt32, ncclSum, ctx->nccl, ctx->compute));
+    CK(cudaMemcpyAsync(&solid, dflag, sizeof(int), cudaMemcpyDeviceToHost, ctx->compute));
+  }
+  CK(cudaStreamSynchronize(ctx->compute));
+  ctx->has_solid = solid > 0;
+  if (ctx->has_solid) {
+    if (!ctx->nbmask) {
+      const size_t bytes = (size_t)g.sites_g * sizeof(uint32_t);
+      CK(cudaMalloc(&ctx->nbmask, bytes));
+      ctx->device_bytes += (int64_t)bytes;
+    }
+    CK(launch_neighbour_bits(g, ctx->mask, ctx->nbmask, ctx->compute));
+    ctx->launches++;
+    // a mask that arrives after the populations (or after some steps): make the static values of the solid
+    // sites agree in both buffers (the ghost planes of f[cur] are refreshed first)
+    TRY(ensure_ghosts(ctx));
+    CK(launch_sync_solid(g, ctx->mask, ctx->f[ctx->cur], ctx->f[1 - ctx->cur], ctx->compute));
+    ctx->launches++;
+  }
+  ctx->rho_wall_valid = false;
+  ctx->force_valid = false;
+  return 0;
+}
+
+// eqDistUnity (eqdist.d:310-315): eqDist of pop = (1, 0, ..., 0) at dv = 0 in the reference's operation order
+void eq_dist_unity(int form, double eq[Q]) {
+  if (form == DLBC_EQDIST_BDIST2) {
+    const double aN1 = 1.0 / 36.0, aN0 = 1.0 / 3.0, cst = 1.0 - 0.0, const1 = aN1 * cst;
+    for (int q = 0; q < Q; q++) eq[q] = (q == 0 ? aN0 * cst : (q < 7 ? 2.0 * (const1 + 0.0) : const1 + 0.0)) * 1.0;
+  } else {
+    for (int q = 0; q < Q; q++) eq[q] = (1.0 * weight(q)) * (1.0 + 0.0 + 0.0 - 0.0);
+  }
+}
+
+// L.force[comp] of the last step into a fresh SoA array [3][sites_g] (the caller frees it): zeros before the
+// first step and without Shan-Chen (resetForce, force.d:165-170)
+int last_force(dlbc_cuda_ctx *ctx, int comp, double **vec_out) {
+  const Geom &g = ctx->g;
+  double *vec = nullptr;
+  const size_t vbytes = (size_t)3 * g.sites_g * sizeof(double);
+  CK(cudaMalloc(&vec, vbytes));
+  int rc = 0;
+  if (!ctx->force_valid || !ctx->cfg.enable_shan_chen) {
+    cudaMemsetAsync(vec, 0, vbytes, ctx->compute);
+  } else {
+    // recompute psi of the last step's post-advection state from the previous buffer (its ghost
+    // planes are still intact), then the force; the hot path never stores either
+    ctx->cur ^= 1;  // f[cur] := the populations the last step read
+    StepLaunch L = make_launch(ctx, ctx->compute);
+    ctx->cur ^= 1;
+    rc = psi_all(ctx, L);
+    if (!rc) {
+      cudaError_t e = kKernels[ctx->cfg.ncomp - 1].force(L, comp, vec, 1, g.nz);
+      ctx->launches++;
+      if (e != cudaSuccess) rc = cuda_fail(ctx, "force_kernel", e);
+    }
+  }
+  if (rc) {
+    cudaFree(vec);
+    vec = nullptr;
+  }
+  *vec_out = vec;
+  return rc;
+}
+
 }  // namespace
 
 // =============================================================================================
@@ -748,36 +825,7 @@ int dlbc_cuda_upload_mask(dlbc_cuda_ctx *ctx, const int32_t *mask, int halo) {
   CK(cudaMemcpyAsync(flags, ctx->flags, sizeof(flags), cudaMemcpyDeviceToHost, ctx->compute));
   CK(cudaStreamSynchronize(ctx->compute));
   ARG(flags[0] == 0, "upload_mask: mask values must be 0 (None) or 1 (Solid) (mask.d:84-93)");
-  int solid = flags[1];
-  if (ctx->cfg.nranks == 1) {
-    CK(launch_ghost_fill_mask(g, ctx->mask, ctx->compute));
-    ctx->launches++;
-  } else {
-    TRY(exchange_planes<uint8_t>(ctx, scalar_xfer(ctx, ctx->mask, 1), ncclUint8, ctx->compute));
-    // every rank must take the same kernel path decisions only for itself; but "has_solid" also
-    // has to cover solids in the neighbours' boundary planes (our ghosts): count globally
-    int *dflag = ctx->flags + 1;
-    NK(nccl_api().AllReduce(dflag, dflag, 1, ncclInt32, ncclSum, ctx->nccl, ctx->compute));
-    CK(cudaMemcpyAsync(&solid, dflag, sizeof(int), cudaMemcpyDeviceToHost, ctx->compute));
-  }
-  CK(cudaStreamSynchronize(ctx->compute));
-  ctx->has_solid = solid > 0;
-  if (ctx->has_solid) {
-    if (!ctx->nbmask) {
-      const size_t bytes = (size_t)g.sites_g * sizeof(uint32_t);
-      CK(cudaMalloc(&ctx->nbmask, bytes));
-      ctx->device_bytes += (int64_t)bytes;
-    }
-    CK(launch_neighbour_bits(g, ctx->mask, ctx->nbmask, ctx->compute));
-    ctx->launches++;
-    // a mask that arrives after the populations (or after some steps): make the static values of the solid
-    // sites agree in both buffers (the ghost planes of f[cur] are refreshed first)
-    TRY(ensure_ghosts(ctx));
-    CK(launch_sync_solid(g, ctx->mask, ctx->f[ctx->cur], ctx->f[1 - ctx->cur], ctx->compute));
-    ctx->launches++;
-  }
-  ctx->rho_wall_valid = false;
-  ctx->force_valid = false;
+  TRY(finish_mask(ctx, flags[1]));
   return release_stage(ctx);
 }
 
@@ -845,32 +893,146 @@ int dlbc_cuda_download_force(dlbc_cuda_ctx *ctx, int comp, double *out, int halo
   TRY(check_ctx(ctx));
   ARG(out && halo >= 0, "download_force: bad argument");
   ARG(comp >= 0 && comp < ctx->cfg.ncomp, "download_force: component out of range");
-  const Geom &g = ctx->g;
   TRY(join_comm(ctx));
   double *vec = nullptr;
-  const size_t vbytes = (size_t)3 * g.sites_g * sizeof(double);
-  CK(cudaMalloc(&vec, vbytes));
-  int rc = 0;
-  if (!ctx->force_valid || !ctx->cfg.enable_shan_chen) {
-    // before the first step / without Shan-Chen: resetForce leaves zeros (force.d:165-170)
-    cudaMemsetAsync(vec, 0, vbytes, ctx->compute);
-  } else {
-    // recompute psi of the last step's post-advection state from the previous buffer (its ghost
-    // planes are still intact), then the force; the hot path never stores either
-    ctx->cur ^= 1;  // f[cur] := the populations the last step read
-    StepLaunch L = make_launch(ctx, ctx->compute);
-    ctx->cur ^= 1;
-    rc = psi_all(ctx, L);
-    if (!rc) {
-      cudaError_t e = kKernels[ctx->cfg.ncomp - 1].force(L, comp, vec, 1, g.nz);
-      ctx->launches++;
-      if (e != cudaSuccess) rc = cuda_fail(ctx, "force_kernel", e);
-    }
-  }
-  if (!rc) rc = download_field(ctx, 3, comp, comp, vec, out, halo);
+  TRY(last_force(ctx, comp, &vec));
+  int rc = download_field(ctx, 3, comp, comp, vec, out, halo);
   cudaStreamSynchronize(ctx->compute);
   cudaFree(vec);
   return rc;
+}
+
+// pressure (density.d:306-326) of the current state, every site
+int dlbc_cuda_download_pressure(dlbc_cuda_ctx *ctx, double *out, int halo) {
+  TRY(check_ctx(ctx));
+  ARG(out && halo >= 0, "download_pressure: bad argument");
+  const Geom &g = ctx->g;
+  TRY(join_comm(ctx));
+  TRY(ensure_stage(ctx, (size_t)g.nx * g.ny * g.nz * sizeof(double)));
+  CK(launch_pressure(g, ctx->f[ctx->cur], ctx->p, ctx->cfg.psi_form, (double *)ctx->stage, ctx->compute));
+  ctx->launches++;
+  const int64_t NY = g.ny + 2 * halo, NZ = g.nz + 2 * halo;
+  TRY(copy_layers<double>(ctx, out + (int64_t)halo * NY * NZ, (double *)ctx->stage, halo, 1, g.nx, false));
+  CK(cudaStreamSynchronize(ctx->compute));
+  return release_stage(ctx);
+}
+
+// corrected velocity (velocity.d:177-185): raw velocity + tau * F / rho with the force of the last step
+int dlbc_cuda_download_corrected_velocity(dlbc_cuda_ctx *ctx, int comp, double *out, int halo) {
+  TRY(check_ctx(ctx));
+  ARG(out && halo >= 0, "download_corrected_velocity: bad argument");
+  ARG(comp >= 0 && comp < ctx->cfg.ncomp, "download_corrected_velocity: component out of range");
+  const Geom &g = ctx->g;
+  TRY(join_comm(ctx));
+  double *vec = nullptr;
+  TRY(last_force(ctx, comp, &vec));
+  int rc = ensure_stage(ctx, (size_t)g.nx * g.ny * g.nz * 3 * sizeof(double));
+  if (!rc) {
+    cudaError_t e = launch_corrected_velocity(g, ctx->f[ctx->cur], ctx->mask, comp, ctx->cfg.tau[comp], vec,
+                                              (double *)ctx->stage, ctx->compute);
+    ctx->launches++;
+    if (e != cudaSuccess) rc = cuda_fail(ctx, "corrected_velocity_kernel", e);
+  }
+  const int64_t NY = g.ny + 2 * halo, NZ = g.nz + 2 * halo;
+  if (!rc) rc = copy_layers<double>(ctx, out + (int64_t)halo * NY * NZ * 3, (double *)ctx->stage, halo, 3, g.nx, false);
+  cudaStreamSynchronize(ctx->compute);
+  cudaFree(vec);
+  if (rc) return rc;
+  return release_stage(ctx);
+}
+
+// volumeAveragedDensity (laplace.d:236-272): mean density of every component over the fluid sites of the cube
+// offset +- half_width (global coordinates, not wrapped: the reference's documented behaviour)
+int dlbc_cuda_volume_averaged_density(dlbc_cuda_ctx *ctx, const int64_t offset[3], int half_width, double *out) {
+  TRY(check_ctx(ctx));
+  ARG(offset && out && half_width >= 0, "volume_averaged_density: bad argument");
+  const Geom &g = ctx->g;
+  const int C = ctx->cfg.ncomp;
+  TRY(join_comm(ctx));
+  int64_t lo[3], hi[3];
+  for (int d = 0; d < 3; d++) {
+    lo[d] = offset[d] - half_width;
+    hi[d] = offset[d] + half_width;
+  }
+  double *res = ctx->partial;  // [2 C] of the reduction scratch
+  CK(launch_cube_density(g, ctx->f[ctx->cur], ctx->mask, C, (int64_t)ctx->cfg.rank * g.nz, lo, hi, res, ctx->compute));
+  ctx->launches++;
+  if (ctx->cfg.nranks > 1) NK(nccl_api().AllReduce(res, res, 2 * C, ncclDouble, ncclSum, ctx->nccl, ctx->compute));
+  double h[2 * DLBC_CUDA_MAX_COMPONENTS];
+  CK(cudaMemcpyAsync(h, res, 2 * C * sizeof(double), cudaMemcpyDeviceToHost, ctx->compute));
+  CK(cudaStreamSynchronize(ctx->compute));
+  for (int c = 0; c < C; c++) out[c] = h[2 * c] / h[2 * c + 1];  // (0 / 0 = NaN for an empty cube, as the reference)
+  return 0;
+}
+
+// ---- initial conditions and geometry generated on the device ----------------------------
+int dlbc_cuda_init_mask(dlbc_cuda_ctx *ctx, int kind, int axis, int wall_offset, int thickness, const int32_t has_wall[6]) {
+  TRY(check_ctx(ctx));
+  ARG(kind >= DLBC_MASK_NONE && kind <= DLBC_MASK_WALLS, "init_mask: bad kind");
+  ARG(axis >= 0 && axis < 3, "init_mask: axis out of range (mask.d:161-163)");
+  ARG(kind != DLBC_MASK_WALLS || has_wall, "init_mask: Walls needs dimensionHasWall");
+  const Geom &g = ctx->g;
+  TRY(join_comm(ctx));
+  int hw[6] = {0, 0, 0, 0, 0, 0};
+  if (has_wall)
+    for (int i = 0; i < 6; i++) hw[i] = has_wall[i] != 0;
+  CK(cudaMemsetAsync(ctx->flags, 0, 2 * sizeof(int), ctx->compute));
+  CK(launch_init_mask(g, kind, axis, wall_offset, thickness, hw, ctx->cfg.gn, (int64_t)ctx->cfg.rank * g.nz, ctx->mask,
+                      ctx->flags + 1, ctx->compute));
+  ctx->launches++;
+  int solid = 0;
+  CK(cudaMemcpyAsync(&solid, ctx->flags + 1, sizeof(int), cudaMemcpyDeviceToHost, ctx->compute));
+  CK(cudaStreamSynchronize(ctx->compute));
+  return finish_mask(ctx, solid);
+}
+
+int dlbc_cuda_init_populations(dlbc_cuda_ctx *ctx, int comp, int kind, double density, double perturb, uint32_t seed,
+                               int64_t skip) {
+  TRY(check_ctx(ctx));
+  ARG(comp >= 0 && comp < ctx->cfg.ncomp, "init_populations: component out of range");
+  ARG(kind >= DLBC_INIT_EQDIST && kind <= DLBC_INIT_EQDIST_PERTURB_FRAC, "init_populations: bad kind");
+  ARG(skip >= 0, "init_populations: negative skip");
+  const Geom &g = ctx->g;
+  TRY(join_comm(ctx));
+  double eq[Q];
+  eq_dist_unity(ctx->cfg.eqdist_form, eq);
+  uint32_t *raw = nullptr;
+  double a = 0.0, b = 0.0;
+  if (kind != DLBC_INIT_EQDIST) {
+    // one draw per site of the rank's full array incl. its halo of 2, in memory order (byElementForward)
+    const int64_t n = (int64_t)(g.nx + 4) * (g.ny + 4) * (g.nz + 4);
+    TRY(ensure_stage(ctx, (size_t)n * sizeof(uint32_t)));
+    raw = (uint32_t *)ctx->stage;
+    CK(launch_mt19937(seed, skip, n, raw, ctx->compute));
+    ctx->launches++;
+    if (kind == DLBC_INIT_EQDIST_RANDOM) {
+      a = 0.0;
+      b = 2.0;
+    } else {
+      a = -perturb;
+      b = perturb;
+    }
+  }
+  CK(launch_init_populations(g, kind, density, a, std::nextafter(b, -INFINITY), eq, raw, comp, ctx->f[ctx->cur],
+                             ctx->f[1 - ctx->cur], ctx->compute));
+  ctx->launches++;
+  CK(cudaStreamSynchronize(ctx->compute));
+  ctx->ghosts_valid = false;
+  ctx->rho_wall_valid = false;
+  ctx->force_valid = false;
+  return release_stage(ctx);
+}
+
+int dlbc_cuda_init_wall(dlbc_cuda_ctx *ctx) {
+  TRY(check_ctx(ctx));
+  TRY(join_comm(ctx));
+  if (ctx->has_solid) {
+    CK(launch_init_wall(ctx->g, ctx->mask, ctx->f[0], ctx->f[1], ctx->compute));
+    ctx->launches++;
+  }
+  ctx->rho_wall_valid = false;
+  ctx->force_valid = false;
+  return 0;
 }
 
 static int reduce_component(dlbc_cuda_ctx *ctx, int comp, double out4[4]) {

@@ -272,6 +272,258 @@ cudaError_t launch_output(const Geom &g, int kind, const double *f, const uint8_
   return cudaGetLastError();
 }
 
+// ---- more derived outputs ----------------------------------------------------------
+// pressure (density.d:306-326): P = css * sum_i (rho_i + sum_j 0.5 * gcc[i][j] * psi(rho_i) * psi(rho_j)),
+// accumulated in the reference's order; computed on every site from the densities found there.
+template <int PSI>
+__global__ void pressure_out_kernel(Geom g, const double *__restrict__ f, StepParams P, double *__restrict__ out) {
+  __shared__ double tile[32][33];
+  const int x0 = blockIdx.x * 32, y = blockIdx.y, z0 = blockIdx.z * 32;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int x = x0 + threadIdx.x, z = z0 + j;
+    if (x >= g.nx || z >= g.nz) continue;
+    double rho[MAXC];
+    for (int c = 0; c < P.ncomp; c++) {
+      double fa[Q];
+      load_site(f, g, c, z + 1, y * g.nx + x, fa);
+      rho[c] = density19(fa);
+    }
+    double pr = 0.0;
+    for (int i = 0; i < P.ncomp; i++) {
+      pr += rho[i];
+      for (int k = 0; k < P.ncomp; k++) pr += 0.5 * P.gcc[i * MAXC + k] * psi_of<PSI>(rho[i]) * psi_of<PSI>(rho[k]);
+    }
+    tile[j][threadIdx.x] = pr * (1.0 / 3.0);
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int x = x0 + j, z = z0 + threadIdx.x;
+    if (x >= g.nx || z >= g.nz) continue;
+    out[((int64_t)x * g.ny + y) * g.nz + z] = tile[threadIdx.x][j];
+  }
+}
+cudaError_t launch_pressure(const Geom &g, const double *f, const StepParams &P, int psi_form, double *out, cudaStream_t s) {
+  dim3 grid((g.nx + 31) / 32, g.ny, (g.nz + 31) / 32), block(32, 8);
+  if (psi_form == 0) pressure_out_kernel<0><<<grid, block, 0, s>>>(g, f, P, out);
+  else pressure_out_kernel<1><<<grid, block, 0, s>>>(g, f, P, out);
+  return cudaGetLastError();
+}
+
+// corrected velocity (velocity.d:177-185): rawVelocity + tau * F / rho per dimension, zero on solid sites (as
+// velocityField, velocity.d:106-117); F = the SoA force field [3][sites_g] of the last step
+__global__ void corrected_velocity_kernel(Geom g, const double *__restrict__ f, const uint8_t *__restrict__ mask, int c,
+                                          double tau, const double *__restrict__ F, double *__restrict__ out) {
+  __shared__ double tile[3][32][33];
+  const int x0 = blockIdx.x * 32, y = blockIdx.y, z0 = blockIdx.z * 32;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int x = x0 + threadIdx.x, z = z0 + j;
+    if (x >= g.nx || z >= g.nz) continue;
+    const int64_t s = ((int64_t)(z + 1) * g.ny + y) * g.nx + x;
+    const bool fluid = mask[s] == 0;
+    double fa[Q], m[3];
+    load_site(f, g, c, z + 1, y * g.nx + x, fa);
+    momentum19(fa, m);
+    const double rho = density19(fa);
+#pragma unroll
+    for (int d = 0; d < 3; d++) {
+      double v = m[d] / rho;
+      v += tau * F[(int64_t)d * g.sites_g + s] / rho;
+      tile[d][j][threadIdx.x] = fluid ? v : 0.0;
+    }
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int x = x0 + j, z = z0 + threadIdx.x;
+    if (x >= g.nx || z >= g.nz) continue;
+    const int64_t o = (((int64_t)x * g.ny + y) * g.nz + z) * 3;
+#pragma unroll
+    for (int d = 0; d < 3; d++) out[o + d] = tile[d][threadIdx.x][j];
+  }
+}
+cudaError_t launch_corrected_velocity(const Geom &g, const double *f, const uint8_t *mask, int c, double tau, const double *F,
+                                      double *out, cudaStream_t s) {
+  dim3 grid((g.nx + 31) / 32, g.ny, (g.nz + 31) / 32), block(32, 8);
+  corrected_velocity_kernel<<<grid, block, 0, s>>>(g, f, mask, c, tau, F, out);
+  return cudaGetLastError();
+}
+
+// volumeAveragedDensity (laplace.d:236-272): sum and count over the fluid sites of the cube [lo, hi] (global
+// coordinates, inclusive, not wrapped) that lie in this slab, in the reference's order (x, y, z; z fastest).
+// out[2 c] = sum, out[2 c + 1] = number of sites.  A handful of sites: one thread.
+__global__ void cube_density_kernel(Geom g, const double *__restrict__ f, const uint8_t *__restrict__ mask, int ncomp,
+                                    int64_t z_first, int64_t lx, int64_t hx, int64_t ly, int64_t hy, int64_t lz, int64_t hz,
+                                    double *__restrict__ out) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  for (int c = 0; c < ncomp; c++) {
+    double sum = 0.0, cnt = 0.0;
+    for (int64_t x = lx < 0 ? 0 : lx; x <= hx && x < g.nx; x++)
+      for (int64_t y = ly < 0 ? 0 : ly; y <= hy && y < g.ny; y++)
+        for (int64_t z = lz < z_first ? z_first : lz; z <= hz && z < z_first + g.nz; z++) {
+          const int zg = (int)(z - z_first) + 1;
+          const int sxy = (int)(y * g.nx + x);
+          if (mask[(int64_t)zg * g.plane + sxy]) continue;
+          double fa[Q];
+          load_site(f, g, c, zg, sxy, fa);
+          sum += density19(fa);
+          cnt += 1.0;
+        }
+    out[2 * c] = sum;
+    out[2 * c + 1] = cnt;
+  }
+}
+cudaError_t launch_cube_density(const Geom &g, const double *f, const uint8_t *mask, int ncomp, int64_t z_first,
+                                const int64_t lo[3], const int64_t hi[3], double *out, cudaStream_t s) {
+  cube_density_kernel<<<1, 32, 0, s>>>(g, f, mask, ncomp, z_first, lo[0], hi[0], lo[1], hi[1], lo[2], hi[2], out);
+  return cudaGetLastError();
+}
+
+// ---- initial conditions and geometry on the device -----------------------------------
+// Mt19937 (Phobos std.random: the standard 32-bit Mersenne Twister, Knuth seeding; random.d:19-26) as ONE block:
+// the 624-word state is regenerated in the three dependent sections of the reference algorithm (words 0..226,
+// 227..453, 454..622, then 623), each section in parallel; tempered outputs skip .. skip + n - 1 are stored.
+constexpr int MT_N = 624, MT_M = 397;
+__global__ void __launch_bounds__(256) mt19937_kernel(uint32_t seed, int64_t skip, int64_t n, uint32_t *__restrict__ out) {
+  __shared__ uint32_t mt[MT_N];
+  if (threadIdx.x == 0) {
+    uint32_t x = seed;
+    mt[0] = x;
+    for (int i = 1; i < MT_N; i++) {
+      x = 1812433253u * (x ^ (x >> 30)) + (uint32_t)i;
+      mt[i] = x;
+    }
+  }
+  __syncthreads();
+  const int64_t end = skip + n;
+  for (int64_t base = 0; base < end; base += MT_N) {
+    // twist: mt[k] = mt[k + M (mod N)] ^ (y >> 1) ^ (y & 1 ? 0x9908b0df : 0), y = upper bit of mt[k] | lower 31 of mt[k + 1]
+    for (int sec = 0; sec < 4; sec++) {
+      const int lo = sec == 0 ? 0 : (sec == 1 ? MT_N - MT_M : (sec == 2 ? 2 * (MT_N - MT_M) : MT_N - 1));
+      const int hi = sec == 0 ? MT_N - MT_M : (sec == 1 ? 2 * (MT_N - MT_M) : (sec == 2 ? MT_N - 1 : MT_N));
+      const int k = lo + (int)threadIdx.x;
+      uint32_t v = 0;
+      if (k < hi) {
+        const uint32_t y = (mt[k] & 0x80000000u) | (mt[k + 1 == MT_N ? 0 : k + 1] & 0x7fffffffu);
+        v = mt[k + MT_M < MT_N ? k + MT_M : k + MT_M - MT_N] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+      }
+      __syncthreads();  // every input of the section is read before any of its words is replaced
+      if (k < hi) mt[k] = v;
+      __syncthreads();
+    }
+    for (int i = threadIdx.x; i < MT_N; i += blockDim.x) {
+      const int64_t idx = base + i;
+      if (idx < skip || idx >= end) continue;
+      uint32_t y = mt[i];
+      y ^= y >> 11;
+      y ^= (y << 7) & 0x9d2c5680u;
+      y ^= (y << 15) & 0xefc60000u;
+      y ^= y >> 18;
+      out[idx - skip] = y;
+    }
+    __syncthreads();
+  }
+}
+cudaError_t launch_mt19937(uint32_t seed, int64_t skip, int64_t n, uint32_t *out, cudaStream_t s) {
+  static_assert(MT_N - MT_M <= 256 && MT_N - 1 - 2 * (MT_N - MT_M) <= 256, "a section per pass of the block");
+  mt19937_kernel<<<1, 256, 0, s>>>(seed, skip, n, out);
+  return cudaGetLastError();
+}
+
+// initEqDist / initEqDistRandom / initEqDistPerturb / initEqDistPerturbFrac (fields/init.d:52-82) for the physical
+// sites of one component, straight into the SoA buffers.  `raw` = the Mt19937 outputs of the reference's draw
+// order: one per site of the rank's FULL array incl. its halo of 2, x slowest, z fastest (byElementForward);
+// uniform(a, b) of Phobos for doubles = a + (nextafter(b, -inf) - a) * raw / 4294967295.0 (dlbc_b200/rng.py).
+// kind 0: rho * eq; 1: rho * u * eq, u in [0, 2); 2: (rho + u) * eq, u in [-p, p); 3: rho * (1 + u) * eq
+struct InitParams {
+  int kind;
+  double density, a, b_below;  // uniform(a, b): b_below = nextafter(b, -inf)
+  double eq[Q];                // eqDistUnity (eqdist.d:310-315)
+};
+__global__ void __launch_bounds__(128) init_populations_kernel(Geom g, InitParams ip, const uint32_t *__restrict__ raw, int c,
+                                                               double *__restrict__ fa, double *__restrict__ fb) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= g.nx) return;
+  const int y = blockIdx.y, zg = blockIdx.z + 1;
+  double rho = ip.density;
+  if (ip.kind != 0) {
+    const int64_t idx = ((int64_t)(x + 2) * (g.ny + 4) + (y + 2)) * (g.nz + 4) + (zg + 1);
+    const double u = ip.a + (ip.b_below - ip.a) * (double)raw[idx] / 4294967295.0;
+    rho = ip.kind == 1 ? ip.density * u : (ip.kind == 2 ? ip.density + u : ip.density * (1.0 + u));
+  }
+  const int64_t base = (int64_t)zg * g.fz + (int64_t)c * g.fc + (int64_t)y * g.nx + x;
+#pragma unroll
+  for (int q = 0; q < Q; q++) {
+    const double v = rho * ip.eq[q];
+    fa[base + (int64_t)qslot(q) * g.plane] = v;
+    fb[base + (int64_t)qslot(q) * g.plane] = v;
+  }
+}
+cudaError_t launch_init_populations(const Geom &g, int kind, double density, double a, double b_below, const double *eq,
+                                    const uint32_t *raw, int c, double *fa, double *fb, cudaStream_t s) {
+  InitParams ip;
+  ip.kind = kind; ip.density = density; ip.a = a; ip.b_below = b_below;
+  for (int q = 0; q < Q; q++) ip.eq[q] = eq[q];
+  const unsigned bx = g.nx >= 128 ? 128 : ((g.nx + 31) / 32) * 32;
+  init_populations_kernel<<<dim3((g.nx + bx - 1) / bx, g.ny, g.nz), bx, 0, s>>>(g, ip, raw, c, fa, fb);
+  return cudaGetLastError();
+}
+
+// initEqDistWall (fields/init.d:469-477): populations of solid sites := (1, 0, ..., 0), every component, both
+// buffers, ghost planes included (their mask is valid after the upload / generation of the mask)
+__global__ void init_wall_kernel(Geom g, const uint8_t *__restrict__ m, double *__restrict__ fa, double *__restrict__ fb) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= g.nx) return;
+  const int y = blockIdx.y, zg = blockIdx.z;
+  const int64_t sxy = (int64_t)y * g.nx + x;
+  if (!m[(int64_t)zg * g.plane + sxy]) return;
+  for (int c = 0; c < g.ncomp; c++)
+    for (int q = 0; q < Q; q++) {
+      const int64_t i = (int64_t)zg * g.fz + (int64_t)c * g.fc + (int64_t)qslot_rt(q) * g.plane + sxy;
+      const double v = q == 0 ? 1.0 : 0.0;
+      fa[i] = v;
+      fb[i] = v;
+    }
+}
+cudaError_t launch_init_wall(const Geom &g, const uint8_t *m, double *fa, double *fb, cudaStream_t s) {
+  const unsigned bx = g.nx >= 128 ? 128 : ((g.nx + 31) / 32) * 32;
+  init_wall_kernel<<<dim3((g.nx + bx - 1) / bx, g.ny, g.nz + 2), bx, 0, s>>>(g, m, fa, fb);
+  return cudaGetLastError();
+}
+
+// initMask (lb/mask.d:134-172; fields/init.d:377-467): kind 0 None, 1 Box, 2 Tube (open along `axis`),
+// 3 Plates (normal to `axis`, `wall_offset` sites in), 4 Walls (per dimension and side, `thickness` sites).
+// Physical planes only, global coordinates (z_first = global z of local plane 1); counts the solid sites.
+struct MaskParams {
+  int kind, axis, wall_offset, thickness;
+  int has_wall[3][2];
+  int64_t gn[3], z_first;
+};
+__global__ void init_mask_kernel(Geom g, MaskParams mp, uint8_t *__restrict__ m, int *__restrict__ nsolid) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= g.nx) return;
+  const int y = blockIdx.y, zg = blockIdx.z + 1;
+  const int64_t p[3] = {x, y, mp.z_first + zg - 1};
+  bool solid = false;
+  for (int d = 0; d < 3; d++) {
+    const bool lo = p[d] == 0, hi = p[d] == mp.gn[d] - 1;
+    if (mp.kind == 1) solid |= lo || hi;
+    else if (mp.kind == 2) solid |= d != mp.axis && (lo || hi);
+    else if (mp.kind == 3) solid |= d == mp.axis && (p[d] == mp.wall_offset || p[d] == mp.gn[d] - 1 - mp.wall_offset);
+    else if (mp.kind == 4) solid |= (mp.has_wall[d][0] && p[d] < mp.thickness) || (mp.has_wall[d][1] && p[d] >= mp.gn[d] - mp.thickness);
+  }
+  m[(int64_t)zg * g.plane + (int64_t)y * g.nx + x] = solid ? 1 : 0;
+  if (solid) atomicAdd(nsolid, 1);
+}
+cudaError_t launch_init_mask(const Geom &g, int kind, int axis, int wall_offset, int thickness, const int has_wall[6],
+                             const int64_t gn[3], int64_t z_first, uint8_t *m, int *nsolid, cudaStream_t s) {
+  MaskParams mp;
+  mp.kind = kind; mp.axis = axis; mp.wall_offset = wall_offset; mp.thickness = thickness;
+  for (int d = 0; d < 3; d++) { mp.has_wall[d][0] = has_wall[2 * d]; mp.has_wall[d][1] = has_wall[2 * d + 1]; mp.gn[d] = gn[d]; }
+  mp.z_first = z_first;
+  const unsigned bx = g.nx >= 128 ? 128 : ((g.nx + 31) / 32) * 32;
+  init_mask_kernel<<<dim3((g.nx + bx - 1) / bx, g.ny, g.nz), bx, 0, s>>>(g, mp, m, nsolid);
+  return cudaGetLastError();
+}
+
 // Own-site densities of every site incl. ghosts, SoA (for the wall term, force.d:298: the density
 // "on the wall" is the sum of the solid site's own, never-advected populations).
 __global__ void site_density_kernel(Geom g, const double *__restrict__ f, int c, double *__restrict__ rho) {

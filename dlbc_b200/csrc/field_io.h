@@ -33,6 +33,22 @@ cudaError_t launch_sync_solid(const Geom &g, const uint8_t *m, const double *src
 // kind 0 density(c1), 1 colour(c1 - c2), 2 raw velocity(c1), 3 copy of an SoA vector field [3][sites_g]
 cudaError_t launch_output(const Geom &g, int kind, const double *f, const uint8_t *mask, int c1, int c2, double *out,
                           cudaStream_t s);
+// pressure (density.d:306-326), corrected velocity (velocity.d:177-185) and the cube sums behind
+// volumeAveragedDensity (laplace.d:236-272): see field_io.cu
+cudaError_t launch_pressure(const Geom &g, const double *f, const StepParams &P, int psi_form, double *out, cudaStream_t s);
+cudaError_t launch_corrected_velocity(const Geom &g, const double *f, const uint8_t *mask, int c, double tau, const double *F,
+                                      double *out, cudaStream_t s);
+cudaError_t launch_cube_density(const Geom &g, const double *f, const uint8_t *mask, int ncomp, int64_t z_first,
+                                const int64_t lo[3], const int64_t hi[3], double *out, cudaStream_t s);
+
+// initial conditions / geometry generated on the device (fields/init.d:52-82,377-477; random.d:19-26)
+cudaError_t launch_mt19937(uint32_t seed, int64_t skip, int64_t n, uint32_t *out, cudaStream_t s);
+cudaError_t launch_init_populations(const Geom &g, int kind, double density, double a, double b_below, const double *eq,
+                                    const uint32_t *raw, int c, double *fa, double *fb, cudaStream_t s);
+cudaError_t launch_init_wall(const Geom &g, const uint8_t *m, double *fa, double *fb, cudaStream_t s);
+cudaError_t launch_init_mask(const Geom &g, int kind, int axis, int wall_offset, int thickness, const int has_wall[6],
+                             const int64_t gn[3], int64_t z_first, uint8_t *m, int *nsolid, cudaStream_t s);
+
 // own-site density of every site incl. ghosts (SoA -> SoA), for the wall term
 cudaError_t launch_site_density(const Geom &g, const double *f, int c, double *rho, cudaStream_t s);
 

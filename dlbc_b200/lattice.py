@@ -186,6 +186,40 @@ class Lattice:
         self._ck(self._l.dlbc_cuda_download_force(self._h, comp, _dp(out), 0))
         return out
 
+    def pressure(self):
+        """density.d:306-326 on every site."""
+        out = np.empty(self.n)
+        self._ck(self._l.dlbc_cuda_download_pressure(self._h, _dp(out), 0))
+        return out
+
+    def corrected_velocity(self, comp):
+        """velocity.d:177-185: raw velocity + tau * F / rho (force of the last step), zero on solid sites."""
+        out = np.empty(self.n + (3,))
+        self._ck(self._l.dlbc_cuda_download_corrected_velocity(self._h, comp, _dp(out), 0))
+        return out
+
+    def volume_averaged_density(self, offset, half_width=1):
+        """laplace.d:236-272: mean density of every component over the fluid sites of the cube offset +- half_width."""
+        off = (C.c_int64 * 3)(*[int(v) for v in offset])
+        out = np.empty(self.ncomp)
+        self._ck(self._l.dlbc_cuda_volume_averaged_density(self._h, off, int(half_width), _dp(out)))
+        return out
+
+    # ---- geometry / initial conditions generated on the device (fields/init.d, lb/mask.d) ----------
+    def init_mask(self, kind="None", axis=0, wall_offset=0, thickness=1, dimension_has_wall=None):
+        hw = None
+        if dimension_has_wall is not None:
+            flat = [int(bool(v)) for row in dimension_has_wall for v in row]
+            hw = (C.c_int32 * 6)(*(flat + [0] * 6)[:6])
+        self._ck(self._l.dlbc_cuda_init_mask(self._h, _lib.MASK_KIND[kind], int(axis), int(wall_offset), int(thickness), hw))
+
+    def init_populations(self, comp, kind, density, perturb=0.0, seed=0, skip=0):
+        self._ck(self._l.dlbc_cuda_init_populations(self._h, int(comp), _lib.INIT_KIND[kind], float(density), float(perturb),
+                                                    int(seed) & 0xFFFFFFFF, int(skip)))
+
+    def init_wall(self):
+        self._ck(self._l.dlbc_cuda_init_wall(self._h))
+
     def total_mass(self, comp):
         v = C.c_double()
         self._ck(self._l.dlbc_cuda_total_mass(self._h, comp, C.byref(v)))

@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.environ.get("DLBC_CUDA_LIB") or os.path.join(HERE, "libdlbc_cuda.so")  # override: A/B runs of two builds
 MAXC = 4
 NCCL_ID_BYTES = 128
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 PSI = {"Linear": 0, "Exponential": 1}
 EQ = {"SecondOrder": 0, "ThirdOrder": 1, "BDist2": 2}
@@ -30,8 +30,11 @@ SYMBOLS = [
     "dlbc_cuda_download_colour", "dlbc_cuda_download_velocity", "dlbc_cuda_download_force",
     "dlbc_cuda_total_mass", "dlbc_cuda_total_momentum", "dlbc_cuda_tables", "dlbc_cuda_launch_count",
     "dlbc_cuda_timed_steps", "dlbc_cuda_kernel_times", "dlbc_cuda_device_bytes", "dlbc_cuda_kernel_variant",
-    "dlbc_cuda_set_option",
+    "dlbc_cuda_set_option", "dlbc_cuda_download_pressure", "dlbc_cuda_download_corrected_velocity",
+    "dlbc_cuda_volume_averaged_density", "dlbc_cuda_init_mask", "dlbc_cuda_init_populations", "dlbc_cuda_init_wall",
 ]
+MASK_KIND = {"None": 0, "Box": 1, "Tube": 2, "Plates": 3, "Walls": 4}
+INIT_KIND = {"EqDist": 0, "EqDistRandom": 1, "EqDistPerturb": 2, "EqDistPerturbFrac": 3}
 
 
 class Config(C.Structure):
@@ -97,6 +100,12 @@ def load():
     L.dlbc_cuda_device_bytes.argtypes = [vp, i64p]
     L.dlbc_cuda_kernel_variant.argtypes = [vp, C.POINTER(C.c_int)]
     L.dlbc_cuda_set_option.argtypes = [vp, C.c_char_p, C.c_int64]
+    L.dlbc_cuda_download_pressure.argtypes = [vp, dp, C.c_int]
+    L.dlbc_cuda_download_corrected_velocity.argtypes = [vp, C.c_int, dp, C.c_int]
+    L.dlbc_cuda_volume_averaged_density.argtypes = [vp, i64p, C.c_int, dp]
+    L.dlbc_cuda_init_mask.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, ip]
+    L.dlbc_cuda_init_populations.argtypes = [vp, C.c_int, C.c_int, C.c_double, C.c_double, C.c_uint32, C.c_int64]
+    L.dlbc_cuda_init_wall.argtypes = [vp]
     for name in SYMBOLS:
         fn = getattr(L, name)
         if name not in ("dlbc_cuda_last_error", "dlbc_cuda_timestep"):

@@ -5,8 +5,9 @@
  * runTimeloop (reference src/main.d:179-195): exchangeHalo -> advectFields -> resetForce ->
  * addShanChenForce -> distributeForce -> prepareToCollide -> collideFields, for the D3Q19
  * lattice, N-component Shan-Chen, BGK, bounce-back walls, periodic boundaries.  Parameter files,
- * plugin registration, mask/geometry setup, initial conditions and HDF5 output stay on the
- * host (D) side; they hand finished arrays to this library and fetch results from it.
+ * plugin registration and HDF5 output stay on the host (D) side, which hands finished arrays to
+ * this library and fetches results from it; mask/geometry setup and initial conditions may come
+ * from the host as arrays or be generated on the device (dlbc_cuda_init_*).
  *
  * Conventions (modelled on how the reference treats its C libraries, src/dlbc/mpi.d:16-18 and
  * src/dlbc/io/hdf5.d:54-57): plain C types only; every function returns int, 0 = success,
@@ -36,7 +37,7 @@
 extern "C" {
 #endif
 
-#define DLBC_CUDA_ABI_VERSION 2
+#define DLBC_CUDA_ABI_VERSION 3
 #define DLBC_CUDA_MAX_COMPONENTS 4
 #define DLBC_CUDA_NCCL_ID_BYTES 128
 
@@ -53,15 +54,15 @@ enum {
 };
 /* step kernel variants (evidence for the design choice; results are identical bit for bit) */
 enum {
-  DLBC_KERNEL_AUTO = 0,       /* TMA where the lattice allows it (nx even; nx % 4 == 0 with solid sites) on one
-                                 rank and on thick z-slabs, else WAVE; TWO_PASS on thin slabs and without
-                                 Shan-Chen */
+  DLBC_KERNEL_AUTO = 0,       /* WAVE on one rank and on thick z-slabs; TWO_PASS on thin slabs and without
+                                 Shan-Chen (measured choice, profiles/README.md) */
   DLBC_KERNEL_TWO_PASS = 1,   /* psi kernel + fused pull/force/collide kernel (psi via L1/L2) */
   DLBC_KERNEL_WAVE = 2,       /* psi sites + fused sites in ONE launch, ticket-ordered band by band so that the
                                  second gather of every population is an L2 hit; per-thread register gathers */
-  DLBC_KERNEL_TMA = 3         /* the same schedule, warp-specialised: a producer warp stages population rows and
-                                 psi rows into shared memory with TMA bulk copies (cp.async.bulk + mbarrier),
-                                 consumer warps compute from shared memory */
+  DLBC_KERNEL_TMA = 3         /* the same schedule, warp-specialised: producer warps stage population rows and
+                                 psi rows into shared memory with tensor-map TMA copies (cp.async.bulk.tensor +
+                                 mbarrier), consumer warps compute from shared memory.  No mask path, even nx,
+                                 at most two components: everything else must use AUTO or WAVE */
 };
 
 /* Replaces: the module-level parameters the timestep reads -- lattice.gn (lattice.d:28),
@@ -123,6 +124,26 @@ int dlbc_cuda_download_populations_xrange(dlbc_cuda_ctx *ctx, int comp, double *
 int dlbc_cuda_upload_mask(dlbc_cuda_ctx *ctx, const int32_t *mask, int halo);
 int dlbc_cuda_download_mask(dlbc_cuda_ctx *ctx, int32_t *mask, int halo);
 
+/* ---- geometry and initial conditions generated on the device ---------------------------------
+ * For lattices whose state should never exist on the host (1024^3 is 326 GB per copy).  Bit-identical to what
+ * the reference's initialisers produce on this rank's block:
+ * init_mask: initMask (lb/mask.d:134-172; fields/init.d:377-467) for MaskInit None / Box / Tube / Plates / Walls;
+ *   `axis` = lb.mask.initAxis, `wall_offset` = wallOffset (Plates), `thickness` = wallThickness and
+ *   has_wall[2 d + side] = dimensionHasWall[d][side] (Walls; may be NULL otherwise).
+ * init_populations: initEqDist / initEqDistRandom / initEqDistPerturb / initEqDistPerturbFrac
+ *   (fields/init.d:52-82) with the context's eqDistForm.  Random kinds draw one Phobos uniform() per site of the
+ *   rank's FULL array including its halo of 2, in memory order (x slowest, z fastest), from Mt19937(seed) after
+ *   discarding `skip` outputs -- seed = randomSeed[f] (+ rank if shiftSeedByRank) with skip = 0 for a reseeding
+ *   fluid (lb/init.d:109-118), else random.seed (+ rank) with skip = the draws earlier fluids consumed.
+ * init_wall: initEqDistWall (fields/init.d:469-477, lb/init.d:121) for every component: populations of solid
+ *   sites := (1, 0, ..., 0).  Call after the mask and the populations are in place. */
+enum { DLBC_MASK_NONE = 0, DLBC_MASK_BOX = 1, DLBC_MASK_TUBE = 2, DLBC_MASK_PLATES = 3, DLBC_MASK_WALLS = 4 };
+enum { DLBC_INIT_EQDIST = 0, DLBC_INIT_EQDIST_RANDOM = 1, DLBC_INIT_EQDIST_PERTURB = 2, DLBC_INIT_EQDIST_PERTURB_FRAC = 3 };
+int dlbc_cuda_init_mask(dlbc_cuda_ctx *ctx, int kind, int axis, int wall_offset, int thickness, const int32_t has_wall[6]);
+int dlbc_cuda_init_populations(dlbc_cuda_ctx *ctx, int comp, int kind, double density, double perturb, uint32_t seed,
+                               int64_t skip);
+int dlbc_cuda_init_wall(dlbc_cuda_ctx *ctx);
+
 /* ---- the hot path ---------------------------------------------------------------------------
  * step replaces the statements of runTimeloop, main.d:179-195, nsteps times.  Asynchronous:
  * returns after enqueueing on the context's streams; sync waits (and reports device errors). */
@@ -139,6 +160,15 @@ int dlbc_cuda_download_density(dlbc_cuda_ctx *ctx, int comp, double *out, int ha
 int dlbc_cuda_download_colour(dlbc_cuda_ctx *ctx, int comp1, int comp2, double *out, int halo);
 int dlbc_cuda_download_velocity(dlbc_cuda_ctx *ctx, int comp, double *out, int halo);
 int dlbc_cuda_download_force(dlbc_cuda_ctx *ctx, int comp, double *out, int halo);
+/* pressure: density.d:306-326 evaluated on every site, P = css * sum_i (rho_i + sum_j 0.5 gcc[i][j] psi_i psi_j).
+ * corrected_velocity: velocity.d:177-185, raw velocity + tau * F / rho with L.force of the last step; zero on
+ * solid sites like velocityField.  volume_averaged_density: laplace.d:236-272, the mean density of every
+ * component over the fluid sites of the cube offset +- half_width (global coordinates, not wrapped, summed in
+ * the reference's site order) -- with total_mass the only lattice data dumpLaplace (laplace.d:55-222) needs, so
+ * Laplace's surface tension is evaluated without downloading a field.  out: ncomp doubles. */
+int dlbc_cuda_download_pressure(dlbc_cuda_ctx *ctx, double *out, int halo);
+int dlbc_cuda_download_corrected_velocity(dlbc_cuda_ctx *ctx, int comp, double *out, int halo);
+int dlbc_cuda_volume_averaged_density(dlbc_cuda_ctx *ctx, const int64_t offset[3], int half_width, double *out);
 /* globalTotalMass (density.d:172-180) / globalTotalMomentum (momentum.d:172-180): sums over
  * physical fluid sites of all ranks; deterministic tree reduction (not the reference's
  * sequential order, so equal only to summation round-off). */
