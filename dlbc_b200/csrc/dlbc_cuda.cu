@@ -1023,6 +1023,44 @@ int dlbc_cuda_init_populations(dlbc_cuda_ctx *ctx, int comp, int kind, double de
   return release_stage(ctx);
 }
 
+int dlbc_cuda_init_spheres(dlbc_cuda_ctx *ctx, int comp, int ncentres, const double *centres, int skip_axis, double radius,
+                           double thickness, double density1, double density2) {
+  TRY(check_ctx(ctx));
+  ARG(comp >= 0 && comp < ctx->cfg.ncomp, "init_spheres: component out of range");
+  ARG(centres && (ncentres == 1 || ncentres == 2), "init_spheres: one or two centres");
+  ARG(skip_axis >= -1 && skip_axis < 3, "init_spheres: bad axis");
+  TRY(join_comm(ctx));
+  double eq[Q];
+  eq_dist_unity(ctx->cfg.eqdist_form, eq);
+  CK(launch_init_profile(ctx->g, 0, ncentres, centres, skip_axis, 0, radius, thickness, density1, density2, nullptr,
+                         (int64_t)ctx->cfg.rank * ctx->g.nz, eq, comp, ctx->f[ctx->cur], ctx->f[1 - ctx->cur], ctx->compute));
+  ctx->launches++;
+  ctx->ghosts_valid = false;
+  ctx->rho_wall_valid = false;
+  ctx->force_valid = false;
+  return 0;
+}
+
+int dlbc_cuda_init_axis_profile(dlbc_cuda_ctx *ctx, int comp, int axis, const double *values) {
+  TRY(check_ctx(ctx));
+  ARG(comp >= 0 && comp < ctx->cfg.ncomp, "init_axis_profile: component out of range");
+  ARG(axis >= 0 && axis < 3 && values, "init_axis_profile: bad argument");
+  TRY(join_comm(ctx));
+  double eq[Q];
+  eq_dist_unity(ctx->cfg.eqdist_form, eq);
+  const size_t bytes = (size_t)ctx->cfg.gn[axis] * sizeof(double);
+  TRY(ensure_stage(ctx, bytes));
+  CK(cudaMemcpyAsync(ctx->stage, values, bytes, cudaMemcpyHostToDevice, ctx->compute));
+  CK(launch_init_profile(ctx->g, 1, 0, nullptr, -1, axis, 0.0, 0.0, 0.0, 0.0, (const double *)ctx->stage,
+                         (int64_t)ctx->cfg.rank * ctx->g.nz, eq, comp, ctx->f[ctx->cur], ctx->f[1 - ctx->cur], ctx->compute));
+  ctx->launches++;
+  CK(cudaStreamSynchronize(ctx->compute));
+  ctx->ghosts_valid = false;
+  ctx->rho_wall_valid = false;
+  ctx->force_valid = false;
+  return 0;
+}
+
 int dlbc_cuda_init_wall(dlbc_cuda_ctx *ctx) {
   TRY(check_ctx(ctx));
   TRY(join_comm(ctx));

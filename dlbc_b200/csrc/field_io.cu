@@ -467,6 +467,67 @@ cudaError_t launch_init_populations(const Geom &g, int kind, double density, dou
   return cudaGetLastError();
 }
 
+// initEqDistSphere / TwoSpheres / Cylinder (fields/init.d:84-259): rho = symmetricLinearTransition(distance to the
+// nearest centre - radius, thickness, d1, d2) (init.d:346-366), distance = sqrt(sum_i (gn_i - centre_i + 0.5)^2)
+// accumulated over i = 0, 1, 2 (the skipped axis of a cylinder contributes 0.0); or (kind 1) the value of a 1-D
+// profile along `axis` (lamellae, init.d:261-313: the host evaluates the profile, gn[axis] numbers).
+struct ProfileParams {
+  int kind;         // 0 spheres / cylinder, 1 axis profile
+  int ncentres, skip_axis, axis;
+  double centre[2][3], radius, width, negval, posval;
+  int64_t z_first;  // global z of local plane 1
+  double eq[Q];
+};
+__device__ __forceinline__ double symmetric_linear_transition(double pos, double width, double negval, double posval) {
+  if (width == 0.0) return pos < 0.0 ? negval : posval;
+  if (pos < -0.5 * width) return negval;
+  if (pos > 0.5 * width) return posval;
+  return negval * (0.5 - pos / width) + posval * (0.5 + pos / width);
+}
+__global__ void __launch_bounds__(128) init_profile_kernel(Geom g, ProfileParams pp, const double *__restrict__ profile, int c,
+                                                           double *__restrict__ fa, double *__restrict__ fb) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= g.nx) return;
+  const int y = blockIdx.y, zg = blockIdx.z + 1;
+  const int64_t p[3] = {x, y, pp.z_first + zg - 1};
+  double rho;
+  if (pp.kind == 1) {
+    rho = profile[p[pp.axis]];
+  } else {
+    double rel = 0.0;
+    for (int k = 0; k < pp.ncentres; k++) {
+      double acc = 0.0;
+      for (int d = 0; d < 3; d++) {
+        const double off = d == pp.skip_axis ? 0.0 : (double)p[d] - pp.centre[k][d] + 0.5;
+        acc = acc + off * off;
+      }
+      const double r = sqrt(acc) - pp.radius;
+      rel = k == 0 ? r : (r < rel ? r : rel);
+    }
+    rho = symmetric_linear_transition(rel, pp.width, pp.negval, pp.posval);
+  }
+  const int64_t base = (int64_t)zg * g.fz + (int64_t)c * g.fc + (int64_t)y * g.nx + x;
+#pragma unroll
+  for (int q = 0; q < Q; q++) {
+    const double v = rho * pp.eq[q];
+    fa[base + (int64_t)qslot(q) * g.plane] = v;
+    fb[base + (int64_t)qslot(q) * g.plane] = v;
+  }
+}
+cudaError_t launch_init_profile(const Geom &g, int kind, int ncentres, const double *centres, int skip_axis, int axis, double radius,
+                                double width, double negval, double posval, const double *profile, int64_t z_first,
+                                const double *eq, int c, double *fa, double *fb, cudaStream_t s) {
+  ProfileParams pp;
+  pp.kind = kind; pp.ncentres = ncentres; pp.skip_axis = skip_axis; pp.axis = axis;
+  for (int k = 0; k < 2; k++)
+    for (int d = 0; d < 3; d++) pp.centre[k][d] = centres && k < ncentres ? centres[3 * k + d] : 0.0;
+  pp.radius = radius; pp.width = width; pp.negval = negval; pp.posval = posval; pp.z_first = z_first;
+  for (int q = 0; q < Q; q++) pp.eq[q] = eq[q];
+  const unsigned bx = g.nx >= 128 ? 128 : ((g.nx + 31) / 32) * 32;
+  init_profile_kernel<<<dim3((g.nx + bx - 1) / bx, g.ny, g.nz), bx, 0, s>>>(g, pp, profile, c, fa, fb);
+  return cudaGetLastError();
+}
+
 // initEqDistWall (fields/init.d:469-477): populations of solid sites := (1, 0, ..., 0), every component, both
 // buffers, ghost planes included (their mask is valid after the upload / generation of the mask)
 __global__ void init_wall_kernel(Geom g, const uint8_t *__restrict__ m, double *__restrict__ fa, double *__restrict__ fb) {

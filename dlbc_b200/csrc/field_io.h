@@ -45,6 +45,9 @@ cudaError_t launch_cube_density(const Geom &g, const double *f, const uint8_t *m
 cudaError_t launch_mt19937(uint32_t seed, int64_t skip, int64_t n, uint32_t *out, cudaStream_t s);
 cudaError_t launch_init_populations(const Geom &g, int kind, double density, double a, double b_below, const double *eq,
                                     const uint32_t *raw, int c, double *fa, double *fb, cudaStream_t s);
+cudaError_t launch_init_profile(const Geom &g, int kind, int ncentres, const double *centres, int skip_axis, int axis, double radius,
+                                double width, double negval, double posval, const double *profile, int64_t z_first,
+                                const double *eq, int c, double *fa, double *fb, cudaStream_t s);
 cudaError_t launch_init_wall(const Geom &g, const uint8_t *m, double *fa, double *fb, cudaStream_t s);
 cudaError_t launch_init_mask(const Geom &g, int kind, int axis, int wall_offset, int thickness, const int has_wall[6],
                              const int64_t gn[3], int64_t z_first, uint8_t *m, int *nsolid, cudaStream_t s);

@@ -217,6 +217,36 @@ class Lattice:
         self._ck(self._l.dlbc_cuda_init_populations(self._h, int(comp), _lib.INIT_KIND[kind], float(density), float(perturb),
                                                     int(seed) & 0xFFFFFFFF, int(skip)))
 
+    def init_spheres(self, comp, density1, density2, radius, thickness, offset=(0, 0, 0), separation=None, cylinder_axis=None,
+                     frac=False):
+        """initEqDistSphere / TwoSpheres (separation given) / Cylinder (cylinder_axis given) and their *Frac variants
+        (fields/init.d:84-259); the scalar arithmetic on the parameters is dlbc_b200.init's."""
+        gn = self.gn
+        if frac:
+            small = min(g for i, g in enumerate(gn) if i != cylinder_axis)
+            radius = radius * small
+            offset = [offset[i] * gn[i] for i in range(3)]
+            if separation is not None:
+                separation = [separation[i] * gn[i] for i in range(3)]
+        if separation is None:
+            centres = [[1 * gn[i] * 0.5 + offset[i] for i in range(3)]]
+        else:
+            centres = [[1 * gn[i] * 0.5 + offset[i] - 0.5 * separation[i] for i in range(3)],
+                       [1 * gn[i] * 0.5 + offset[i] + 0.5 * separation[i] for i in range(3)]]
+        flat = np.array(centres, dtype=np.float64).ravel()
+        self._ck(self._l.dlbc_cuda_init_spheres(self._h, int(comp), len(centres), _dp(flat),
+                                                -1 if cylinder_axis is None else int(cylinder_axis), float(radius),
+                                                float(thickness), float(density1), float(density2)))
+
+    def init_lamellae(self, comp, values, widths, axis, thickness, frac=False):
+        """initEqDistLamellae(Frac) (fields/init.d:261-313): the 1-D profile is evaluated on the host."""
+        from . import init as I
+        if frac:
+            widths = [w * self.gn[axis] for w in widths]
+        line = I.Block((self.gn[axis],) * 3, halo=0)
+        prof = np.ascontiguousarray(I.lamellae_values(line, values, widths, 0, thickness)[:, 0, 0], dtype=np.float64)
+        self._ck(self._l.dlbc_cuda_init_axis_profile(self._h, int(comp), int(axis), _dp(prof)))
+
     def init_wall(self):
         self._ck(self._l.dlbc_cuda_init_wall(self._h))
 

@@ -32,6 +32,7 @@ SYMBOLS = [
     "dlbc_cuda_timed_steps", "dlbc_cuda_kernel_times", "dlbc_cuda_device_bytes", "dlbc_cuda_kernel_variant",
     "dlbc_cuda_set_option", "dlbc_cuda_download_pressure", "dlbc_cuda_download_corrected_velocity",
     "dlbc_cuda_volume_averaged_density", "dlbc_cuda_init_mask", "dlbc_cuda_init_populations", "dlbc_cuda_init_wall",
+    "dlbc_cuda_init_spheres", "dlbc_cuda_init_axis_profile",
 ]
 MASK_KIND = {"None": 0, "Box": 1, "Tube": 2, "Plates": 3, "Walls": 4}
 INIT_KIND = {"EqDist": 0, "EqDistRandom": 1, "EqDistPerturb": 2, "EqDistPerturbFrac": 3}
@@ -106,6 +107,8 @@ def load():
     L.dlbc_cuda_init_mask.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, ip]
     L.dlbc_cuda_init_populations.argtypes = [vp, C.c_int, C.c_int, C.c_double, C.c_double, C.c_uint32, C.c_int64]
     L.dlbc_cuda_init_wall.argtypes = [vp]
+    L.dlbc_cuda_init_spheres.argtypes = [vp, C.c_int, C.c_int, dp, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double]
+    L.dlbc_cuda_init_axis_profile.argtypes = [vp, C.c_int, C.c_int, dp]
     for name in SYMBOLS:
         fn = getattr(L, name)
         if name not in ("dlbc_cuda_last_error", "dlbc_cuda_timestep"):

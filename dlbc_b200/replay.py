@@ -140,6 +140,54 @@ def initial_populations(p, blk, mask):
     return pops
 
 
+def device_initialise(L, p):
+    """initMask + initFluids + initEqDistWall generated ON THE DEVICE (dlbc_cuda_init_*): no host
+    array of the lattice's size ever exists.  One-rank semantics as `initial_populations`; raises ReplayError for the
+    initialisers the device does not generate (Const, ConstRandom, File)."""
+    C = int(p["lb.components"])
+    gn = tuple(int(x) for x in p["lattice.gn"])
+    kind = p["lb.mask.maskInit"]
+    if kind not in ("None", "Box", "Tube", "Plates", "Walls"):
+        raise ReplayError(f"lb.mask.maskInit = {kind} is not generated on the device")
+    dhw = None
+    if kind == "Walls":
+        dhw = [_fit(x, 2, "lb.mask.dimensionHasWall[i]", fill=False)
+               for x in _fit(p["lb.mask.dimensionHasWall"], 3, "lb.mask.dimensionHasWall", fill=[False, False])]
+    L.init_mask(kind, axis=AXIS[p["lb.mask.initAxis"]], wall_offset=p["lb.mask.wallOffset"],
+                thickness=p["lb.mask.wallThickness"], dimension_has_wall=dhw)
+    kinds = _fit(p["lb.init.fluidInit"], C, "lb.init.fluidInit", fill="None")
+    dens = _fit(p["lb.init.fluidDensities"], C, "lb.init.fluidDensities", fill=[])
+    perturb = _fit(p["lb.init.fluidPerturb"], C, "lb.init.fluidPerturb", fill=0.0)
+    reseed = _fit(p["lb.init.randomReseed"], C, "lb.init.randomReseed", fill=False)
+    seeds = _fit(p["lb.init.randomSeed"], C, "lb.init.randomSeed", fill=0)
+    off = _fit(p["lb.init.initOffset"], 3, "lb.init.initOffset", fill=0.0)
+    sep = _fit(p["lb.init.initSeparation"], 3, "lb.init.initSeparation", fill=0.0)
+    axis = AXIS[p["lb.init.initAxis"]]
+    radius, thick = p["lb.init.initRadius"], p["lb.init.interfaceThickness"]
+    widths = list(p["lb.init.lamellaeWidths"])
+    nfull = (gn[0] + 4) * (gn[1] + 4) * (gn[2] + 4)  # draws one random initialiser takes from its generator
+    shared_draws = 0                                   # consumed so far from the global generator (random.d:43-53)
+    for f in range(C):
+        k, d = kinds[f], list(dens[f])
+        frac = k.endswith("Frac")
+        if k in ("EqDist", "EqDistRandom", "EqDistPerturb", "EqDistPerturbFrac"):
+            seed, skip = (seeds[f], 0) if reseed[f] else (p["random.seed"], shared_draws)
+            L.init_populations(f, k, d[0], perturb=perturb[f], seed=seed, skip=skip)
+            if k != "EqDist" and not reseed[f]:
+                shared_draws += nfull
+        elif k in ("EqDistSphere", "EqDistSphereFrac"):
+            L.init_spheres(f, d[0], d[1], radius, thick, offset=off, frac=frac)
+        elif k in ("EqDistTwoSpheres", "EqDistTwoSpheresFrac"):
+            L.init_spheres(f, d[0], d[1], radius, thick, offset=off, separation=sep, frac=frac)
+        elif k in ("EqDistCylinder", "EqDistCylinderFrac"):
+            L.init_spheres(f, d[0], d[1], radius, thick, offset=off, cylinder_axis=axis, frac=frac)
+        elif k in ("EqDistLamellae", "EqDistLamellaeFrac"):
+            L.init_lamellae(f, d, widths, axis, thick, frac=frac)
+        else:
+            raise ReplayError(f"lb.init.fluidInit[{f}] = {k} is not generated on the device")
+    L.init_wall()  # lb/init.d:121
+
+
 def _dump_now(freq, t):
     """io/io.d:224-226"""
     return freq > 0 and t % freq == 0
@@ -182,21 +230,26 @@ def _cuda_lattice(gn, C, kw, device=0, arithmetic="fast", kernel="auto"):
     return Lattice(gn, C, **kw, device=device, arithmetic=arithmetic, kernel=kernel)
 
 
-def replay(p, make_lattice=None, **lattice_options):
+def replay(p, make_lattice=None, device_init=False, **lattice_options):
     """Run the case described by parameter dict `p`; returns {file-name stem: array}.
-    make_lattice(gn, components, kwargs) -> object with the `Lattice` interface (default: the CUDA library)."""
+    make_lattice(gn, components, kwargs) -> object with the `Lattice` interface (default: the CUDA library).
+    device_init: generate mask and initial populations on the device instead of uploading host arrays."""
     gn, C, kw = lattice_kwargs(p)
     names = _fit(p["lb.fieldNames"], C, "lb.lb.fieldNames", strict=True)
     p = dict(p, **{"lb.fieldNames": names})
     blk = I.Block(gn)
-    mask = initial_mask(p, blk)
-    pops = initial_populations(p, blk, mask)
+    if not device_init:
+        mask = initial_mask(p, blk)
+        pops = initial_populations(p, blk, mask)
     L = make_lattice(gn, C, kw) if make_lattice else _cuda_lattice(gn, C, kw, **lattice_options)
     out = {}
     try:
-        L.set_mask(mask, halo=blk.halo)
-        for c, a in enumerate(pops):
-            L.set_populations(c, a, halo=blk.halo)
+        if device_init:
+            device_initialise(L, p)
+        else:
+            L.set_mask(mask, halo=blk.halo)
+            for c, a in enumerate(pops):
+                L.set_populations(c, a, halo=blk.halo)
         if hasattr(L, "exchange_halo"):
             L.exchange_halo()  # main.d:142 (the CUDA library maintains its ghost planes itself)
         _collect(L, p, 0, out)  # "First data dump", main.d:149
@@ -235,9 +288,11 @@ def main(argv=None):
     ap.add_argument("--run-id", default="00000000T000000", help="time-stamp id in the file names (io/io.d:157-172)")
     ap.add_argument("--arith", default="fast", choices=["fast", "exact"])
     ap.add_argument("--device", type=int, default=0)
+    ap.add_argument("--device-init", action="store_true",
+                    help="generate mask and initial populations on the GPU (dlbc_cuda_init_*) instead of uploading them")
     a = ap.parse_args(argv)
     p = P.parse_file(a.parameter_file, a.parameter)
-    out = replay(p, arithmetic=a.arith, device=a.device)
+    out = replay(p, device_init=a.device_init, arithmetic=a.arith, device=a.device)
     for k, v in out.items():
         print(f"{k}: shape {v.shape}, sum {float(np.sum(v)):.15g}")
     if a.out:

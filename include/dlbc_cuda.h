@@ -142,6 +142,15 @@ enum { DLBC_INIT_EQDIST = 0, DLBC_INIT_EQDIST_RANDOM = 1, DLBC_INIT_EQDIST_PERTU
 int dlbc_cuda_init_mask(dlbc_cuda_ctx *ctx, int kind, int axis, int wall_offset, int thickness, const int32_t has_wall[6]);
 int dlbc_cuda_init_populations(dlbc_cuda_ctx *ctx, int comp, int kind, double density, double perturb, uint32_t seed,
                                int64_t skip);
+/* init_spheres: initEqDistSphere / TwoSpheres / Cylinder (fields/init.d:84-259): density1 within `radius` of the
+ * nearest of the 1 or 2 centres (global coordinates, centres[3 k + d] = nc n / 2 + initOffset -+ initSeparation / 2),
+ * density2 outside, a linear transition `thickness` wide (init.d:346-366); skip_axis >= 0 makes it a cylinder
+ * along that axis (-1: spheres).  The *Frac variants are the same call with the host's scaled radius / offsets.
+ * init_axis_profile: a density that depends on the coordinate along `axis` only (initEqDistLamellae,
+ * init.d:261-313: the host evaluates the gn[axis] profile values). */
+int dlbc_cuda_init_spheres(dlbc_cuda_ctx *ctx, int comp, int ncentres, const double *centres, int skip_axis, double radius,
+                           double thickness, double density1, double density2);
+int dlbc_cuda_init_axis_profile(dlbc_cuda_ctx *ctx, int comp, int axis, const double *values);
 int dlbc_cuda_init_wall(dlbc_cuda_ctx *ctx);
 
 /* ---- the hot path ---------------------------------------------------------------------------

@@ -159,6 +159,24 @@ def test_init_populations_on_device_bitexact(gn):
         assert_bitexact(G.get_populations(0), w, "device EqDist")
 
 
+def test_init_profiles_on_device_bitexact():
+    """spheres, two spheres, cylinder and lamellae (fields/init.d:84-313) generated on the device == host restatement."""
+    gn = (20, 16, 24)
+    blk = I.Block(gn)
+    it = blk.interior()
+    with Lattice(gn, 4, tau=[1.0] * 4, eqdist_form="BDist2") as G:
+        G.init_spheres(0, 0.7, 0.04, 0.25, 5.0, frac=True)                                               # laplace-droplet-3d
+        G.init_spheres(1, 0.04, 0.7, 0.2, 5.0, separation=[0.4, 0, 0], frac=True)                       # merging-droplets-3d
+        G.init_spheres(2, 0.5, 0.1, 4.5, 0.0, offset=[1.0, -2.0, 0.5], cylinder_axis=1)                 # sharp cylinder
+        G.init_lamellae(3, [0.7, 0.04, 0.3], [0.25, 0.5, 0.25], 2, 3.0, frac=True)                      # bdist2-sc-3d style
+        want = [I.init_eq_dist_sphere_frac(blk, d3q19, I.BDIST2, 0.7, 0.04, 0.25, [0, 0, 0], 5.0),
+                I.init_eq_dist_two_spheres_frac(blk, d3q19, I.BDIST2, 0.04, 0.7, 0.2, [0, 0, 0], 5.0, [0.4, 0, 0]),
+                I.init_eq_dist_cylinder(blk, d3q19, I.BDIST2, 0.5, 0.1, 1, 4.5, [1.0, -2.0, 0.5], 0.0),
+                I.init_eq_dist_lamellae_frac(blk, d3q19, I.BDIST2, [0.7, 0.04, 0.3], [0.25, 0.5, 0.25], 2, 3.0)]
+        for c in range(4):
+            assert_bitexact(G.get_populations(c), np.ascontiguousarray(want[c][it]), f"device profile init {c}")
+
+
 def test_spinodal_from_device_init_matches_host_init():
     """BASELINE configs[2] twin started from device-generated populations steps exactly like the host-initialised one."""
     params, pops, _ = cases.spinodal(32)

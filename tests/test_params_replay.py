@@ -147,6 +147,21 @@ def test_replay_reference_case_on_the_gpu(golden, case, times):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("case,times", [("merging-droplets-3d", (0, 10)), ("bdist2-3d", (0, 10)),
+                                        ("bdist2-sc-3d", (0, 10)), ("laplace-droplet-3d", (0, 10))])
+def test_replay_reference_case_with_device_side_init(golden, case, times):
+    """the same cases with mask and initial populations generated on the device: identical
+    outputs, bit for bit, to the host-initialised replay, and within tolerance of the reference's goldens."""
+    p = P.parse_file(os.path.join(IN, case + ".in"), FAST[case])
+    out = R.replay(p, device_init=True)
+    _check(case, out, golden(case), "rel", times)
+    host = R.replay(p)
+    assert out.keys() == host.keys()
+    for k in out:
+        assert np.array_equal(out[k], host[k]), k
+
+
+@pytest.mark.gpu
 def test_replay_full_length_cases_on_the_gpu(golden):
     """bdist2-sc-3d unmodified (100 steps, populations) and laplace-droplet-3d to t = 100."""
     p = P.parse_file(os.path.join(IN, "bdist2-sc-3d.in"))
