@@ -1119,6 +1119,26 @@ int dlbc_cuda_tables(int64_t *velocities, int64_t *bounce_out, double *weights, 
   return 0;
 }
 
+int dlbc_cuda_site_function(int device, int fn, int form, int n, const double *in, const double *in2, double *out) {
+  dlbc_cuda_ctx *ctx = nullptr;
+  ARG(fn >= DLBC_SITE_DENSITY && fn <= DLBC_SITE_EQDIST && n >= 0 && in && out, "site_function: bad argument");
+  ARG(fn != DLBC_SITE_EQDIST || in2, "site_function: the equilibrium needs the velocity shifts dv[n][3]");
+  ARG(form >= 0 && form <= 2 && (fn != DLBC_SITE_PSI || form <= 1), "site_function: bad form");
+  if (n == 0) return 0;
+  CK(cudaSetDevice(device));
+  const size_t nin = (size_t)n * (fn == DLBC_SITE_PSI ? 1 : Q), nout = (size_t)n * (fn == DLBC_SITE_VELOCITY ? 3 : fn == DLBC_SITE_EQDIST ? Q : 1);
+  const size_t nin2 = !in2 ? 0 : (size_t)n * (fn == DLBC_SITE_EQDIST ? 3 : 1);
+  double *d = nullptr;
+  CK(cudaMalloc(&d, (nin + nin2 + nout) * sizeof(double)));
+  cudaError_t e = cudaMemcpy(d, in, nin * sizeof(double), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess && nin2) e = cudaMemcpy(d + nin, in2, nin2 * sizeof(double), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = launch_site_function(fn, form, n, d, nin2 ? d + nin : nullptr, d + nin + nin2, nullptr);
+  if (e == cudaSuccess) e = cudaMemcpy(out, d + nin + nin2, nout * sizeof(double), cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (e != cudaSuccess) return cuda_fail(nullptr, "site_function", e);
+  return 0;
+}
+
 int dlbc_cuda_launch_count(const dlbc_cuda_ctx *ctx, int64_t *count) {
   if (!ctx || !count) return 1;
   *count = ctx->launches;

@@ -272,6 +272,45 @@ cudaError_t launch_output(const Geom &g, int kind, const double *f, const uint8_
   return cudaGetLastError();
 }
 
+// ---- the per-site device functions, one site at a time ---------------------------------------------------
+// For the reference's in-source known-answer tests (density.d:50-61, velocity.d:59-74, force.d:370-384,
+// eqdist.d:317-360): evaluates the functions of lb_site.cuh -- the ones every step kernel is built from, in their
+// EXACT instantiation -- on n sites given as pop[n][19] (+ dv[n][3] for the equilibrium).
+//   fn 0: density19 -> out[n];  1: raw velocity (momentum19 / rho, rho = in2[i] if given else density19) -> out[n][3];
+//   2: psi_of<form>(in[i]) -> out[n];  3: equilibrium distribution of `form` with shift dv = in2[i] -> out[n][19]
+__global__ void site_function_kernel(int fn, int form, int n, const double *__restrict__ in, const double *__restrict__ in2,
+                                     double *__restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (fn == 2) {
+    out[i] = form == 0 ? psi_of<0>(in[i]) : psi_of<1>(in[i]);
+    return;
+  }
+  double f[Q];
+  for (int q = 0; q < Q; q++) f[q] = in[(int64_t)i * Q + q];
+  if (fn == 0) {
+    out[i] = density19(f);
+  } else if (fn == 1) {
+    double m[3];
+    momentum19(f, m);
+    const double rho = in2 ? in2[i] : density19(f);
+    for (int d = 0; d < 3; d++) out[(int64_t)i * 3 + d] = m[d] / rho;
+  } else {
+    double m[3], dv[3], eq[Q];
+    momentum19(f, m);
+    for (int d = 0; d < 3; d++) dv[d] = in2[(int64_t)i * 3 + d];
+    const double rho = density19(f);
+    if (form == 0) eqdist_poly<0, true>(m, dv, rho, eq);
+    else if (form == 1) eqdist_poly<1, true>(m, dv, rho, eq);
+    else eqdist_bdist2(dv, rho, eq);
+    for (int q = 0; q < Q; q++) out[(int64_t)i * Q + q] = eq[q];
+  }
+}
+cudaError_t launch_site_function(int fn, int form, int n, const double *in, const double *in2, double *out, cudaStream_t s) {
+  site_function_kernel<<<(n + 127) / 128, 128, 0, s>>>(fn, form, n, in, in2, out);
+  return cudaGetLastError();
+}
+
 // ---- more derived outputs ----------------------------------------------------------
 // pressure (density.d:306-326): P = css * sum_i (rho_i + sum_j 0.5 * gcc[i][j] * psi(rho_i) * psi(rho_j)),
 // accumulated in the reference's order; computed on every site from the densities found there.

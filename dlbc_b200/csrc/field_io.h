@@ -41,6 +41,9 @@ cudaError_t launch_corrected_velocity(const Geom &g, const double *f, const uint
 cudaError_t launch_cube_density(const Geom &g, const double *f, const uint8_t *mask, int ncomp, int64_t z_first,
                                 const int64_t lo[3], const int64_t hi[3], double *out, cudaStream_t s);
 
+// lb_site.cuh's per-site functions on n sites (known-answer tests): see field_io.cu
+cudaError_t launch_site_function(int fn, int form, int n, const double *in, const double *in2, double *out, cudaStream_t s);
+
 // initial conditions / geometry generated on the device (fields/init.d:52-82,377-477; random.d:19-26)
 cudaError_t launch_mt19937(uint32_t seed, int64_t skip, int64_t n, uint32_t *out, cudaStream_t s);
 cudaError_t launch_init_populations(const Geom &g, int kind, double density, double a, double b_below, const double *eq,

@@ -32,7 +32,7 @@ SYMBOLS = [
     "dlbc_cuda_timed_steps", "dlbc_cuda_kernel_times", "dlbc_cuda_device_bytes", "dlbc_cuda_kernel_variant",
     "dlbc_cuda_set_option", "dlbc_cuda_download_pressure", "dlbc_cuda_download_corrected_velocity",
     "dlbc_cuda_volume_averaged_density", "dlbc_cuda_init_mask", "dlbc_cuda_init_populations", "dlbc_cuda_init_wall",
-    "dlbc_cuda_init_spheres", "dlbc_cuda_init_axis_profile",
+    "dlbc_cuda_init_spheres", "dlbc_cuda_init_axis_profile", "dlbc_cuda_site_function",
 ]
 MASK_KIND = {"None": 0, "Box": 1, "Tube": 2, "Plates": 3, "Walls": 4}
 INIT_KIND = {"EqDist": 0, "EqDistRandom": 1, "EqDistPerturb": 2, "EqDistPerturbFrac": 3}
@@ -109,6 +109,7 @@ def load():
     L.dlbc_cuda_init_wall.argtypes = [vp]
     L.dlbc_cuda_init_spheres.argtypes = [vp, C.c_int, C.c_int, dp, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double]
     L.dlbc_cuda_init_axis_profile.argtypes = [vp, C.c_int, C.c_int, dp]
+    L.dlbc_cuda_site_function.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, dp, dp, dp]
     for name in SYMBOLS:
         fn = getattr(L, name)
         if name not in ("dlbc_cuda_last_error", "dlbc_cuda_timestep"):
@@ -143,3 +144,21 @@ def tables():
     load().dlbc_cuda_tables(v.ctypes.data_as(C.POINTER(C.c_int64)), b.ctypes.data_as(C.POINTER(C.c_int64)),
                             w.ctypes.data_as(C.POINTER(C.c_double)), C.byref(css))
     return v, b, w, css.value
+
+
+def site_function(fn, pops_or_rho, form=0, extra=None, device=0):
+    """lb_site.cuh's per-site functions on the device: fn in "density", "velocity", "psi", "eqdist" (dlbc_cuda_site_function)."""
+    import numpy as np
+    code = {"density": 0, "velocity": 1, "psi": 2, "eqdist": 3}[fn]
+    a = np.ascontiguousarray(np.atleast_1d(np.asarray(pops_or_rho, dtype=np.float64)))
+    n = a.size if code == 2 else a.size // 19
+    if isinstance(form, str):
+        form = (PSI if code == 2 else EQ)[form]
+    out = np.empty({0: (n,), 1: (n, 3), 2: (n,), 3: (n, 19)}[code])
+    dp = C.POINTER(C.c_double)
+    e = None if extra is None else np.ascontiguousarray(np.asarray(extra, dtype=np.float64))
+    rc = load().dlbc_cuda_site_function(device, code, int(form), n, a.ctypes.data_as(dp),
+                                        None if e is None else e.ctypes.data_as(dp), out.ctypes.data_as(dp))
+    if rc:
+        raise DlbcCudaError(load().dlbc_cuda_last_error(None).decode())
+    return out

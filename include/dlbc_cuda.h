@@ -192,6 +192,13 @@ int dlbc_cuda_total_momentum(dlbc_cuda_ctx *ctx, int comp, double out[3]);
  * every kernel; fills names/ms for up to `cap` kernels and returns how many in *n. */
 int dlbc_cuda_tables(int64_t *velocities, int64_t *bounce, double *weights, double *css);
 int dlbc_cuda_launch_count(const dlbc_cuda_ctx *ctx, int64_t *count);
+/* site_function: the per-site device functions every step kernel is built from (csrc/lb_site.cuh, EXACT
+ * instantiation) on n sites, for the reference's in-source known-answer tests -- density (density.d:37-39,50-61),
+ * raw velocity (velocity.d:37-48,59-74; in2 = n pre-computed densities or NULL), psi (force.d:320-332,370-384; in =
+ * n densities, form = DLBC_PSI_*), equilibrium distribution (eqdist.d:61-184,317-360; in2 = dv[n][3], form =
+ * DLBC_EQDIST_*).  in = pop[n][19] except for psi.  Host pointers; no context needed. */
+enum { DLBC_SITE_DENSITY = 0, DLBC_SITE_VELOCITY = 1, DLBC_SITE_PSI = 2, DLBC_SITE_EQDIST = 3 };
+int dlbc_cuda_site_function(int device, int fn, int form, int n, const double *in, const double *in2, double *out);
 int dlbc_cuda_timed_steps(dlbc_cuda_ctx *ctx, int nsteps, double *elapsed_ms);
 int dlbc_cuda_kernel_times(dlbc_cuda_ctx *ctx, int cap, const char **names, double *ms, int *n);
 int dlbc_cuda_device_bytes(const dlbc_cuda_ctx *ctx, int64_t *bytes);

@@ -80,6 +80,38 @@ def test_tables_bitexact():
     assert (v == d3q19.velocities).all()
 
 
+# ---- the reference's in-source known-answer tests against the DEVICE site functions (lb_site.cuh) -------------
+def test_site_function_kats_on_device():
+    pop7 = np.zeros(19); pop7[7] = 0.1
+    pop5 = np.array([0.1, 0.0, 0.1, 0.0, 0.0, 0.0, 0.0, 0.1, 0.0, 0.0, 0.1, 0.0, 0.0, 0.0, 0.1, 0.0, 0.0, 0.0, 0.0])
+    # lb/density.d:50-61
+    assert list(dlib.site_function("density", np.stack([pop7, pop5]))) == [0.1, 0.5]
+    # lb/velocity.d:59-74 (the second with the pre-computed density 0.5), :196-217 through rawVelocity
+    assert list(dlib.site_function("velocity", pop7)[0]) == [1, 1, 0]
+    assert list(dlib.site_function("velocity", pop5, extra=[0.5])[0]) == [-0.2, -0.2, 0.2]
+    # lb/force.d:370-384
+    rho = np.array([0.0, 0.7, 1.0, 2.0])
+    assert list(dlib.site_function("psi", rho, "Linear")) == [0.0, 0.7, 1.0, 2.0]
+    e = dlib.site_function("psi", rho, "Exponential")
+    assert e[0] == 0.0 and np.allclose(e[1:], [0.5034146962, 0.63212055882, 0.86466471676], atol=1e-9, rtol=0)
+    # lb/eqdist.d:317-360: mass conserved; momentum conserved up to the shift dv (not BDist2); eqDistUnity
+    rng = np.random.default_rng(7)
+    pops = rng.random((20, 19))
+    dv = np.full((20, 3), 0.001)
+    for form in ("SecondOrder", "ThirdOrder", "BDist2"):
+        eq = dlib.site_function("eqdist", pops, form, extra=dv)
+        assert np.max(np.abs(dlib.site_function("density", eq) - dlib.site_function("density", pops))) < 1e-12
+        if form != "BDist2":
+            assert np.allclose(dlib.site_function("velocity", eq) - dv, dlib.site_function("velocity", pops), atol=1e-12)
+        for i in range(20):  # the device functions against the oracle's, site by site
+            assert_close(eq[i], O.site_eqdist(form, pops[i], dv[i]), what=f"eqdist {form}")
+        unity = dlib.site_function("eqdist", np.eye(19)[0], form, extra=np.zeros((1, 3)))[0]
+        assert abs(unity.sum() - 1.0) < 1e-15
+        assert_bitexact(unity, I.eq_dist_unity(d3q19, dlib.EQ[form]), "eqDistUnity host vs device")
+    for p in pops:
+        assert dlib.site_function("density", p)[0] == O.site_density(p)
+
+
 def test_upload_download_roundtrip_bitexact():
     rng = np.random.default_rng(1)
     gn = (20, 12, 9)

@@ -61,7 +61,7 @@ def test_reader_overrides_apply_after_the_file():
     assert p["lb.init.fluidInit"] == ["EqDistTwoSpheresFrac"] * 2 and p["lb.init.initSeparation"] == [0.4, 0.0, 0.0]
 
 
-@pytest.mark.parametrize("name", sorted(os.listdir(IN)))
+@pytest.mark.parametrize("name", sorted(n for n in os.listdir(IN) if n.endswith(".in")))
 def test_reader_accepts_every_fixture(name):
     p = P.parse_file(os.path.join(IN, name))
     gn, C, kw = R.lattice_kwargs(p)
@@ -134,6 +134,49 @@ def test_replay_reference_case_on_the_oracle(golden, case, times, tol):
     g = golden(case)
     _check(case, {k: v for k, v in out.items() if k.endswith("t00000000")}, {k: v for k, v in g.items() if k.endswith("-t0")}, 0, (0,))
     _check(case, out, g, tol, times)
+
+
+# ---- the reference's JSON test specifications (dlbct/test.py, compare.py) ------------------------------------
+SPECS = ["merging-droplets-3d", "bdist2-3d", "bdist2-sc-3d", "laplace-droplet-3d"]
+
+
+def test_spec_reader():
+    from dlbc_b200.testspec import SpecError, TestSpec
+    s = TestSpec(os.path.join(IN, "merging-droplets-3d.json"))
+    assert s.configuration == "d3q19" and s.input_file == "merging-droplets-3d.in" and s.np == 1
+    assert s.overrides("fast") == ["lb.timesteps=10", "lb.io.colourFreq=10", "lb.io.densityFreq=10"]
+    assert s.overrides("coverage") == ["lb.timesteps=1"] and s.overrides("full") == []
+    assert ("density-red", 10, 1e-15) in s.compare_rules("fast") and ("density-red", 0, None) in s.compare_rules("fast")
+    assert ("density-blue", 1000, 1e-14) in s.compare_rules("full")
+    assert s.subtests() == [[]]
+    c = TestSpec(os.path.join(IN, "checkpoint-3d.json"))
+    assert c.checkpoint == {"name": "checkpoint-3d-t00000000"} and c.input_file.endswith(".h5")
+    with pytest.raises(SpecError):
+        TestSpec(os.path.join(IN, "merging-droplets-3d.in"))  # not JSON
+
+
+@pytest.mark.parametrize("case", SPECS)
+def test_spec_driven_replay_on_the_oracle(golden, case):
+    """the fast run of each 3-D spec, its OWN overrides and compare rules (exact at t = 0, `accuracy` absolute later)."""
+    from dlbc_b200.testspec import TestSpec
+    extra = ["lb.io.laplaceFreq=0"] if case == "laplace-droplet-3d" else []
+    # floor: the oracle is gcc's arithmetic, "another compiler" than the DMD that wrote the goldens (the laplace spec
+    # carries no accuracy for its fast run; the others grant exactly this 1e-15)
+    rep = TestSpec(os.path.join(IN, case + ".json")).run(golden(case), "fast", subtest=extra, make_lattice=_oracle_lattice,
+                                                         floor=1e-15)
+    assert any(t == 10 for _, t, _, _ in rep) and all(d == 0.0 for _, t, d, _ in rep if t == 0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", SPECS)
+def test_spec_driven_replay_on_the_gpu(golden, case):
+    """the same through libdlbc_cuda in EXACT arithmetic: exact at t = 0; afterwards the spec's accuracy, with the
+    floor the GPU needs as "another compiler" (its exp() is not Phobos': <= 1 ulp per psi, 1e-15 absolute after
+    10 steps -- the bound the reference itself grants non-DMD builds)."""
+    from dlbc_b200.testspec import TestSpec
+    extra = ["lb.io.laplaceFreq=0"] if case == "laplace-droplet-3d" else []
+    rep = TestSpec(os.path.join(IN, case + ".json")).run(golden(case), "fast", subtest=extra, arithmetic="exact", floor=1e-15)
+    assert any(t == 10 for _, t, _, _ in rep) and all(d == 0.0 for _, t, d, _ in rep if t == 0)
 
 
 # ---- replay: GPU ------------------------------------------------------------------------------------
