@@ -118,28 +118,71 @@ def cpu_port_mlups(sample_n, steps, warmup, ncomp=2):
     return sample_n ** 3 * steps / dt * 1e-6, dt, cores
 
 
+def workload_config(args, world, gn, gl, ncomp, porous):
+    """The `config` object both arms print (the reference arm times a bounded SAMPLE of this workload)."""
+    sites_local = gl[0] * gl[1] * gl[2]
+    return {"workload": ("D3Q19 two-fluid Shan-Chen flow through a random porous bounce-back geometry, "
+                         "30 % solid (BASELINE configs[3])" if porous else
+                         "D3Q19 two-component Shan-Chen spinodal decomposition (BASELINE configs[2])"
+                         if ncomp == 2 else "D3Q19 single-fluid BGK periodic (BASELINE configs[1])"),
+            "lattice": list(gn), "components": ncomp, "decomposition": f"{world} z-slab(s) of {list(gl)}",
+            "arithmetic": args.arith, "kernel": args.kernel,
+            "l2": "inputs exceed L2 (populations are %.1f GB per GPU)" % (2 * ncomp * 19 * 8 * sites_local / 1e9)}
+
+
+def bench_lattice(args, world):
+    n = args.size
+    strong = args.scaling == "strong"
+    gn = (n, n, n if strong else n * world)   # weak: `size`^3 per GPU stacked in z; strong: `size`^3 in total
+    if args.shape:
+        sx, sy, sz = (int(v) for v in args.shape.split(","))
+        gn = (sx, sy, sz if strong else sz * world)
+    return gn, (gn[0], gn[1], gn[2] // world)
+
+
+def cpu_config1_mlups(steps):
+    """BASELINE configs[0] as the reference names it: merging-droplets-3d (64^3) on 4 ranks -> 4 oracle threads."""
+    from dlbc_b200 import cases
+    from oracle import oracle as O
+    params, pops, _ = cases.merging_droplets(64)
+    p = dict(params)
+    gn, nc = p.pop("gn"), p.pop("components")
+    L = O.OracleLattice(gn, nc, **p, nthreads=4)
+    for c, a in enumerate(pops):
+        L.set_populations(c, a)
+    L.exchange_halo()
+    L.step(3)
+    t0 = time.perf_counter()
+    L.step(steps)
+    dt = time.perf_counter() - t0
+    return 64 ** 3 * steps / dt * 1e-6, dt
+
+
 def run_reference(args, rank):
+    """The reference's CPU algorithm (oracle port: the D reference cannot be built here) on all host cores, same
+    metric / config / steps / warm-up as our arm; each step runs on a bounded sample of the workload."""
     if rank != 0:
         return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     n = args.cpu_sample
-    # size the timed run to a few tens of seconds: calibrate on 2 steps
+    steps, warmup = max(args.steps, 1), max(args.warmup, 0)
+    # size the sample so that warm-up + timed steps stay within ~2 minutes: calibrate on 2 steps
     mlups, dt, cores = cpu_port_mlups(n, 2, 1)
     per_step = dt / 2
-    steps = max(args.steps, 1)
     budget = 120.0
-    if steps * per_step > budget:
-        n = max(32, int(n * (budget / (steps * per_step)) ** (1 / 3)) // 16 * 16)
-    mlups, dt, cores = cpu_port_mlups(n, steps, min(args.warmup, 3))
+    if (steps + warmup) * per_step > budget:
+        n = max(32, int(n * (budget / ((steps + warmup) * per_step)) ** (1 / 3)) // 16 * 16)
+    mlups, dt, cores = cpu_port_mlups(n, steps, warmup)
+    gn, gl = bench_lattice(args, world)
     line = {
         "impl": "reference", "metric": METRIC, "value": mlups, "unit": "MLUPS", "n_gpus": args.gpus,
-        "steps": steps, "warmup": min(args.warmup, 3), "ms_per_step": 1e3 * dt / steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "D3Q19 two-component Shan-Chen spinodal decomposition (BASELINE configs[2])",
-                   "lattice": [n, n, n], "components": 2, "note": "CPU restatement of the DLBC timestep "
-                   "(oracle/, OpenMP x-slabs standing in for MPI ranks); the D reference needs dmd/ldc/gdc + MPICH + "
-                   "parallel HDF5, none of which exist in this image"},
+        "steps": steps, "warmup": warmup, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True,
+        "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, world, gn, gl, args.components, args.workload == "porous"),
         "cpu_baseline": {"value": mlups, "unit": "MLUPS", "cores": cores, "kind": "port",
-                         "sample": f"{n}^3 sample of the 512^3 workload, {steps} timesteps"},
+                         "sample": f"{n}^3 sample of the workload, {steps} timesteps after {warmup} warm-up steps, {dt:.1f} s; "
+                                   "CPU restatement of the DLBC timestep (oracle/, OpenMP x-slabs standing in for MPI ranks): "
+                                   "the D reference needs dmd/ldc/gdc + MPICH + parallel HDF5, none of which exist in this image"},
         "e2e": {"value": mlups, "unit": "MLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -284,13 +327,8 @@ def run_ours(args, rank, world, local_rank):
         decomp = decomposition_check(args, dist, rank, world, local_rank, dlib)
         log(f"rank {rank}: decomposition check {decomp}")
 
-    n = args.size
     ncomp = args.components
-    strong = args.scaling == "strong"
-    gn = (n, n, n if strong else n * world)   # weak: `size`^3 per GPU stacked in z; strong: `size`^3 in total
-    if args.shape:
-        sx, sy, sz = (int(v) for v in args.shape.split(","))
-        gn = (sx, sy, sz if strong else sz * world)
+    gn, _ = bench_lattice(args, world)
     params = dict(cases.SC2) if ncomp == 2 else dict(tau=[1.0], eqdist_form="SecondOrder", enable_shan_chen=False)
     porous = args.workload == "porous"
     if porous:
@@ -318,9 +356,10 @@ def run_ours(args, rank, world, local_rank):
         v[...] = cases.synthetic_layers(gl, xc, rho0, 0.01, form, 42 + 7 * rank + k)
         views.append(v); ptrs.append(p)
     if porous:
-        # BASELINE configs[3]: random bounce-back geometry (30 % solid, synthetic PCG64 draw), fluids at
+        # BASELINE configs[3]: random bounce-back geometry (solid where u < 0.3, u the
+        # Mt19937(1234 [+ rank]) uniform(0, 1) stream over the physical lattice in [x][y][z] order), fluids at
         # rho = 0.7 / 0.04, solid sites initialised as initEqDistWall does (fields/init.d:469-477)
-        mask = (np.random.default_rng(1234 + rank).random(gl) < 0.3).astype(np.int32)
+        mask = cases.porous_mask(gl, 0.3, 1234 + rank)
         G.set_mask(mask)
         wall = np.zeros(19); wall[0] = 1.0
         eq = I.eq_dist_unity(cases.d3q19, form)
@@ -332,7 +371,7 @@ def run_ours(args, rank, world, local_rank):
                 blk[mask[x0:x0 + cnt] != 0] = wall
                 G.set_populations_xrange(c, blk, x0)
                 G.sync()
-        args.no_e2e = True
+        args.no_e2e = True  # (the e2e leg re-uploads the spinodal layers: not this workload's state)
     else:
         fill_lattice(G, gl, ncomp, views)
     G.sync()
@@ -417,6 +456,23 @@ def run_ours(args, rank, world, local_rank):
                "seconds": dt, "upload_seconds": t_up, "what": "pinned-host upload of all populations + K steps + download of all density fields"}
         lib.dlbc_cuda_host_free(dptr)
 
+    # ---- the same start without host arrays: populations generated on the device ----
+    # NOT the e2e number (its inputs never cross PCIe); reported beside it.
+    dev_init = None
+    if not args.no_e2e and not porous:
+        barrier()
+        t0 = time.perf_counter()
+        for c in range(ncomp):
+            G.init_populations(c, "EqDistPerturb", rho0, perturb=0.01, seed=42 + c + 7 * rank)
+        G.sync()
+        t_init = max_over_ranks(time.perf_counter() - t0)
+        G.step(args.steps, sync=False)
+        G.sync()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        dev_init = {"init_seconds": t_init, "value": sites_total * args.steps / dt * 1e-6, "unit": "MLUPS", "seconds": dt,
+                    "what": "dlbc_cuda_init_populations (EqDistPerturb, Mt19937 in the reference's draw order, per rank) "
+                            "+ K steps; no host buffers, so not an e2e number"}
+
     mass = [G.total_mass(c) for c in range(ncomp)]
     variant = G.kernel_variant
     G.close()
@@ -433,21 +489,20 @@ def run_ours(args, rank, world, local_rank):
         m, dt, cores = cpu_port_mlups(args.cpu_sample, args.cpu_steps, 1)
         cpu = {"value": m, "unit": "MLUPS", "cores": cores, "kind": "port",
                "sample": f"{args.cpu_sample}^3 sample of the workload, {args.cpu_steps} timesteps, {dt:.1f} s"}
+        try:  # BASELINE configs[0]: merging-droplets-3d, 64^3, 4 threads standing in for `mpirun -np 4`
+            m1, dt1 = cpu_config1_mlups(20)
+            cpu["config0_merging_droplets_64cubed_4_threads"] = {"value": m1, "unit": "MLUPS", "seconds": dt1, "steps": 20}
+        except Exception as e:  # noqa: BLE001
+            cpu["config0_merging_droplets_64cubed_4_threads"] = {"error": str(e)}
 
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": "MLUPS", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": ("D3Q19 two-fluid Shan-Chen flow through a random porous bounce-back geometry, "
-                                    "30 % solid (BASELINE configs[3])" if porous else
-                                    "D3Q19 two-component Shan-Chen spinodal decomposition (BASELINE configs[2])"
-                                    if ncomp == 2 else "D3Q19 single-fluid BGK periodic (BASELINE configs[1])"),
-                       "lattice": list(gn), "components": ncomp, "decomposition": f"{world} z-slab(s) of {list(gl)}",
-                       "arithmetic": args.arith, "kernel": args.kernel,
-                       "l2": "inputs exceed L2 (populations are %.1f GB per GPU)" % (2 * ncomp * 19 * 8 * sites_local / 1e9)},
+            "config": workload_config(args, world, gn, gl, ncomp, porous),
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-            "total_mass": mass, "kernel_variant": variant, "parity_check": parity, "decomposition_invariant": decomp,
+            "device_init": dev_init, "total_mass": mass, "kernel_variant": variant, "parity_check": parity, "decomposition_invariant": decomp,
         }
         print(json.dumps(line), flush=True)
     if dist is not None:
