@@ -209,6 +209,78 @@ class _File:
             out[tuple(sl_out)] = chunk[tuple(sl_in)]
 
 
+def _parse_attribute(f, body):
+    """Attribute message v1 (the only version the reference's files carry): name, datatype, dataspace, data."""
+    if body[0] != 1:
+        raise H5Error(f"attribute message version {body[0]} unsupported (need 1)")
+    nsz, tsz, ssz = struct.unpack_from("<HHH", body, 2)
+    o = 8
+    name = bytes(body[o:o + nsz]).split(b"\0")[0].decode()
+    o += (nsz + 7) // 8 * 8
+    dt = body[o:o + tsz]
+    o += (tsz + 7) // 8 * 8
+    ds = body[o:o + ssz]
+    o += (ssz + 7) // 8 * 8
+    rank = ds[1]
+    dims = struct.unpack_from(f"<{rank}Q", ds, 8) if rank else ()
+    n = int(np.prod(dims)) if rank else 1
+    cls, size = dt[0] & 0xF, struct.unpack_from("<I", dt, 4)[0]
+    if cls == 9 and (dt[1] & 0xF) == 1:  # variable-length string: (length u32, global heap collection u64, index u32)
+        vals = []
+        for i in range(n):
+            ln, addr, idx = struct.unpack_from("<IQI", body, o + 16 * i)
+            vals.append(f._gheap_object(addr, idx)[:ln].split(b"\0")[0].decode() if addr not in (0, _UNDEF) else "")
+        return name, vals
+    if cls == 0 and size in (1, 2, 4, 8):
+        signed = bool(dt[1] & 0x08)
+        code = {1: "b", 2: "h", 4: "i", 8: "q"}[size]
+        vals = list(struct.unpack_from("<" + str(n) + (code if signed else code.upper()), body, o))
+        return name, vals[0] if n == 1 else vals
+    if cls == 1 and size == 8:
+        vals = list(struct.unpack_from(f"<{n}d", body, o))
+        return name, vals[0] if n == 1 else vals
+    raise H5Error(f"attribute {name}: datatype class {cls} size {size} unsupported")
+
+
+def _gheap_object(self, addr, index):
+    """Object `index` of the global heap collection at `addr` (variable-length data lives there)."""
+    if self.b[addr:addr + 4] != b"GCOL":
+        raise H5Error("bad global heap signature")
+    end = addr + self.u64(addr + 8)
+    o = addr + 16
+    while o + 16 <= end:
+        idx, size = self.u16(o), self.u64(o + 8)
+        if idx == index:
+            return self.b[o + 16:o + 16 + size]
+        if idx == 0:
+            break
+        o += 16 + (size + 7) // 8 * 8
+    raise H5Error(f"global heap object {index} not found")
+
+
+_File._gheap_object = _gheap_object
+
+
+def read_attributes(path, group=None):
+    """Attributes of the root group (group=None) or of the group /<group> as {name: value}: variable-length string
+    attributes become lists of str (the reference's `input` attribute: the lines of the parameter file,
+    io/hdf5.d:529-548; `metadata/revision*`, :290-299), integers / doubles scalars (`globals/dlbc.lb.lb.timestep`,
+    io/checkpoint.d:248-313)."""
+    f = _File(path)
+    entry = f.root
+    if group is not None:
+        links = f.links()
+        if group not in links:
+            raise H5Error(f"{path}: no group /{group} (have {sorted(links)})")
+        entry = links[group]
+    out = {}
+    for typ, body in f.messages(entry["ohdr"]):
+        if typ == 0x0C:
+            k, v = _parse_attribute(f, body)
+            out[k] = v
+    return out
+
+
 def read_dataset(path, name="OutArray"):
     """Return dataset ``/<name>`` of an HDF5 file as a numpy array (C order)."""
     f = _File(path)
@@ -227,8 +299,8 @@ def list_root(path):
 # dataset /OutArray in an old-style root group.  Superblock v0, object headers v1, dataspace v1, data layout
 # v3 -- the same on-disk structures the reference's own files use (read back by this module's reader and
 # laid out like the libhdf5-written golden files; there is no libhdf5 in this image to cross-check with).
-# Not written: the "input"/"metadata"/"globals" attribute groups of hdf5.d:453-548 (h5diff on /OutArray,
-# which is what the reference's test harness runs, does not look at them).
+# Also written (write_file): the `input` attribute, the `metadata` group and, for checkpoints, the `globals`
+# group of hdf5.d:264-299,453-548 and checkpoint.d:248-313, in the encodings found in the reference's own files.
 
 def _pad8(b):
     return b + b"\0" * (-len(b) % 8)
@@ -253,8 +325,65 @@ def _datatype(dtype):
     raise H5Error(f"dtype {dtype} unsupported (need <f8 or <i4)")
 
 
-def write_dataset(path, array, name="OutArray"):
-    """Write `array` (float64 or int32, C order) as the contiguous dataset /<name> of a new HDF5 file."""
+_VLEN_STR = struct.pack("<B3BI", 0x19, 0x01, 0x00, 0x00, 16) + struct.pack("<B3BIHH", 0x10, 0, 0, 0, 1, 0, 8)  # as libhdf5 encodes it
+_INT32 = struct.pack("<B3BI", 0x10, 0x08, 0x00, 0x00, 4) + struct.pack("<HH", 0, 32)
+_SPACE_1D = lambda n: struct.pack("<BBBx4x", 1, 1, 1) + struct.pack("<QQ", n, n)  # noqa: E731  (v1, max dims present)
+
+
+class _GlobalHeap:
+    """One global heap collection: the variable-length strings of every attribute of the file."""
+
+    def __init__(self):
+        self.objs = []
+
+    def add(self, data):
+        self.objs.append(data)
+        return len(self.objs)  # indices start at 1
+
+    def size(self):
+        n = 16 + sum(16 + (len(d) + 7) // 8 * 8 for d in self.objs) + 16  # header, objects, the free-space object 0
+        return max(4096, (n + 7) // 8 * 8)
+
+    def bytes(self):
+        body = b""
+        for i, d in enumerate(self.objs):
+            body += struct.pack("<HH4xQ", i + 1, 0, len(d)) + _pad8(d)
+        total = self.size()
+        free = total - 16 - len(body)
+        body += struct.pack("<HH4xQ", 0, 0, free) + b"\0" * (free - 16)
+        return b"GCOL" + struct.pack("<B3xQ", 1, total) + body
+
+
+def _attr_msg(name, datatype, nelem, data):
+    nm = name.encode() + b"\0"
+    space = _SPACE_1D(nelem)
+    body = struct.pack("<BxHHH", 1, len(nm), len(datatype), len(space)) + _pad8(nm) + _pad8(datatype) + _pad8(space) + data
+    if len(body) > 65528:
+        raise H5Error(f"attribute {name} does not fit an object header message ({len(body)} bytes)")
+    return _msg(0x0C, body)
+
+
+def _string_attr(name, strings, gheap, gheap_addr_slot):
+    """vlen-string attribute; the heap address is not known yet: `gheap_addr_slot` collects (message, offsets) to patch."""
+    data = b""
+    for st in strings:
+        raw = st.encode() + b"\0"
+        data += struct.pack("<IQI", len(raw), 0, gheap.add(raw))
+    m = bytearray(_attr_msg(name, _VLEN_STR, len(strings), data))
+    first = len(m) - len(_pad8(data))
+    gheap_addr_slot.append((m, [first + 16 * i + 4 for i in range(len(strings))]))
+    return m
+
+
+def write_file(path, array, name="OutArray", input_lines=None, metadata=None, globals_=None):
+    """Write `array` (float64 or int32, C order) as the contiguous dataset /<name> of a new HDF5 file, with the
+    attributes the reference adds to every field file (io/hdf5.d:264-285): `input` on the root group -- the lines of
+    the parameter file, from which the reference can re-read its parameters (parameters.d:172-174,339-351) --, the
+    group `metadata` with string / int attributes (revision info, hdf5.d:290-299) and, for checkpoint files, the
+    group `globals` with int attributes (`dlbc.lb.lb.timestep`, io/checkpoint.d:248-313).
+    Same structures, byte for byte where it matters, as the libhdf5-written files under the reference's
+    reference-data (superblock v0, object header v1, attribute message v1, variable-length strings in a global
+    heap collection, old-style groups with a B-tree and a local heap)."""
     a = np.ascontiguousarray(array)
     if a.dtype == np.float64:
         a = a.astype("<f8", copy=False)
@@ -263,43 +392,107 @@ def write_dataset(path, array, name="OutArray"):
     else:
         raise H5Error(f"dtype {a.dtype} unsupported (need float64 or int32)")
     K_LEAF, K_INT = 4, 16
-    nm = name.encode() + b"\0"
-    heap_data = _pad8(b"\0") + _pad8(nm)                       # offset 0: "", offset 8: name
-    name_off = 8
-    o_root = 96
-    root = _ohdr([_msg(0x11, struct.pack("<QQ", 0, 0))])        # patched below
-    o_btree = o_root + len(root)
+    gheap, patches = _GlobalHeap(), []
+    groups = {}
+    if metadata is not None:
+        groups["metadata"] = metadata
+    if globals_ is not None:
+        groups["globals"] = globals_
+    names = sorted([name] + list(groups))  # symbol node entries are sorted by name
+    heap_data, name_off = _pad8(b"\0"), {}
+    for nm in names:
+        name_off[nm] = len(heap_data)
+        heap_data += _pad8(nm.encode() + b"\0")
     btree_size = 24 + (2 * K_INT + 1) * 8 + 2 * K_INT * 8
-    o_heap = o_btree + btree_size
-    o_heap_data = o_heap + 32
-    o_snod = o_heap_data + len(heap_data)
     snod_size = 8 + 2 * K_LEAF * 40
-    o_dset = o_snod + snod_size
+
+    def attr_msgs(attrs):
+        out = []
+        for k, v in attrs.items():
+            if isinstance(v, str):
+                out.append(_string_attr(k, [v], gheap, patches))
+            elif isinstance(v, (list, tuple)) and all(isinstance(x, str) for x in v):
+                out.append(_string_attr(k, list(v), gheap, patches))
+            elif isinstance(v, (bool, int, np.integer)):
+                out.append(bytearray(_attr_msg(k, _INT32, 1, struct.pack("<i", int(v)))))
+            else:
+                raise H5Error(f"attribute {k}: unsupported value {v!r}")
+        return out
+
+    root_attrs = attr_msgs({"input": list(input_lines)} if input_lines is not None else {})
+    group_attrs = {g: attr_msgs(at) for g, at in groups.items()}
+    # ---- layout --------------------------------------------------------------------------------------------
+    o = 96
+    o_root = o
+    root_len = 16 + 24 + sum(len(m) for m in root_attrs)
+    o += root_len
+    o_btree = o; o += btree_size
+    o_heap = o; o += 32
+    o_heap_data = o; o += len(heap_data)
+    o_snod = o; o += snod_size
+    gpos = {}
+    for g in groups:
+        glen = 16 + 24 + sum(len(m) for m in group_attrs[g])
+        gpos[g] = dict(ohdr=o, btree=o + glen, heap=o + glen + btree_size, heap_data=o + glen + btree_size + 32)
+        o += glen + btree_size + 32 + 8
+    o_dset = o
     rank = a.ndim
     dataspace = struct.pack("<BBBx4x", 1, rank, 0) + struct.pack(f"<{rank}Q", *a.shape)
     fill = bytes([2, 2, 2, 1, 0, 0, 0, 0])                      # v2: late allocation, fill if set, default value
-    layout_len = len(_msg(0x08, struct.pack("<BBQQ", 3, 1, 0, 0)))
-    dset_len = 16 + len(_msg(0x01, dataspace)) + len(_msg(0x03, _datatype(a.dtype))) + len(_msg(0x05, fill)) + layout_len
-    o_data = (o_dset + dset_len + 7) // 8 * 8
+    dset_len = 16 + len(_msg(0x01, dataspace)) + len(_msg(0x03, _datatype(a.dtype))) + len(_msg(0x05, fill)) + \
+        len(_msg(0x08, struct.pack("<BBQQ", 3, 1, 0, 0)))
+    o += dset_len
+    o_gheap = (o + 7) // 8 * 8
+    o = o_gheap + (gheap.size() if gheap.objs else 0)
+    o_data = (o + 7) // 8 * 8
     eof = o_data + a.nbytes
-    dset = _ohdr([_msg(0x01, dataspace), _msg(0x03, _datatype(a.dtype)), _msg(0x05, fill),
-                  _msg(0x08, struct.pack("<BBQQ", 3, 1, o_data, a.nbytes))])
-    assert len(dset) == dset_len
-    root = _ohdr([_msg(0x11, struct.pack("<QQ", o_btree, o_heap))])
+    for m, offs in patches:
+        for k in offs:
+            struct.pack_into("<Q", m, k, o_gheap)
+    # ---- pieces --------------------------------------------------------------------------------------------
     sb = _SIG + bytes([0, 0, 0, 0, 0, 8, 8, 0]) + struct.pack("<HHI", K_LEAF, K_INT, 0)
     sb += struct.pack("<QQQQ", 0, _UNDEF, eof, _UNDEF)
     sb += struct.pack("<QQI4xQQ", 0, o_root, 1, o_btree, o_heap)  # root group symbol table entry
     assert len(sb) == 96
-    btree = b"TREE" + struct.pack("<BBHQQ", 0, 0, 1, _UNDEF, _UNDEF) + struct.pack("<QQQ", 0, o_snod, name_off)
+    root = _ohdr([_msg(0x11, struct.pack("<QQ", o_btree, o_heap))] + [bytes(m) for m in root_attrs])
+    assert len(root) == root_len
+    btree = b"TREE" + struct.pack("<BBHQQ", 0, 0, 1, _UNDEF, _UNDEF) + struct.pack("<QQQ", 0, o_snod, name_off[names[-1]])
     btree += b"\0" * (btree_size - len(btree))
     heap = b"HEAP" + struct.pack("<B3xQQQ", 0, len(heap_data), 1, o_heap_data)  # free-list head 1 = none
-    snod = b"SNOD" + struct.pack("<BxH", 1, 1) + struct.pack("<QQI4x16x", name_off, o_dset, 0)
+    snod = b"SNOD" + struct.pack("<BxH", 1, len(names))
+    for nm in names:
+        if nm in groups:
+            snod += struct.pack("<QQI4xQQ", name_off[nm], gpos[nm]["ohdr"], 1, gpos[nm]["btree"], gpos[nm]["heap"])
+        else:
+            snod += struct.pack("<QQI4x16x", name_off[nm], o_dset, 0)
     snod += b"\0" * (snod_size - len(snod))
+    blob = sb + root + btree + heap + heap_data + snod
+    for g in groups:
+        gp = gpos[g]
+        gh = _ohdr([_msg(0x11, struct.pack("<QQ", gp["btree"], gp["heap"]))] + [bytes(m) for m in group_attrs[g]])
+        gb = b"TREE" + struct.pack("<BBHQQ", 0, 0, 0, _UNDEF, _UNDEF) + struct.pack("<Q", 0)  # an empty leaf: no links
+        gb += b"\0" * (btree_size - len(gb))
+        ghp = b"HEAP" + struct.pack("<B3xQQQ", 0, 8, 1, gp["heap_data"]) + b"\0" * 8
+        assert len(blob) == gp["ohdr"]
+        blob += gh + gb + ghp
+    assert len(blob) == o_dset
+    dset = _ohdr([_msg(0x01, dataspace), _msg(0x03, _datatype(a.dtype)), _msg(0x05, fill),
+                  _msg(0x08, struct.pack("<BBQQ", 3, 1, o_data, a.nbytes))])
+    assert len(dset) == dset_len
+    blob += dset
+    blob += b"\0" * (o_gheap - len(blob))
+    if gheap.objs:
+        blob += gheap.bytes()
+    blob += b"\0" * (o_data - len(blob))
     with open(path, "wb") as fh:
-        fh.write(sb + root + btree + heap + heap_data + snod + dset)
-        fh.write(b"\0" * (o_data - (o_dset + dset_len)))
+        fh.write(blob)
         fh.write(a.tobytes())
     return path
+
+
+def write_dataset(path, array, name="OutArray"):
+    """A bare contiguous dataset /<name> (no attributes)."""
+    return write_file(path, array, name)
 
 
 def field_file_name(field, simulation_name, timestep, time_id="00000000T000000"):

@@ -222,9 +222,22 @@ def parse_text(text, overrides=(), params=None):
     return params
 
 
-def parse_file(path, overrides=()):
+def read_lines(path):
+    """The lines of a parameter file.  An HDF5 file written by the reference (or by dlbc_b200.h5lite.write_file)
+    carries the parameter file it was produced with as the `input` attribute of its root group and can be used
+    in its place (parameters.d:172-174,339-351; io/hdf5.d:529-548)."""
+    if str(path).endswith(".h5"):
+        from . import h5lite
+        attrs = h5lite.read_attributes(path)
+        if "input" not in attrs:
+            raise ParameterError(f"{path}: no 'input' attribute to read the parameters from")
+        return [str(x) for x in attrs["input"]]
     with open(path) as f:
-        return parse_text(f.read(), overrides)
+        return f.read().splitlines()
+
+
+def parse_file(path, overrides=()):
+    return parse_text("\n".join(read_lines(path)) + "\n", overrides)
 
 
 def _to_string(v):

@@ -225,20 +225,71 @@ def _collect(L, p, t, out):
         put("mask", L.get_mask())
 
 
+def checkpoint_paths(p, restore, base_dir="."):
+    """readCheckpoint's file names (io/checkpoint.d:80-103,217-241): <outputPath>/<cpRestorePath>/cp-fluids<i>-<name>.h5
+    and cp-mask-<name>.h5, relative to the directory the reference would be started in."""
+    C = int(p["lb.components"])
+    d = os.path.normpath(os.path.join(base_dir, p["io.outputPath"], p["io.checkpoint.cpRestorePath"]))
+    return [os.path.join(d, f"cp-fluids{i}-{restore}.h5") for i in range(C)], os.path.join(d, f"cp-mask-{restore}.h5")
+
+
+def read_checkpoint(p, restore, base_dir="."):
+    """-> (mask int32 [x][y][z], populations per fluid [x][y][z][19], timestep) of checkpoint `restore`
+    (the reference's `-r <name>`; dlbc.lb.lb.timestep comes from the `globals` group, checkpoint.d:248-313)."""
+    from . import h5lite
+    fluids, maskf = checkpoint_paths(p, restore, base_dir)
+    pops = [h5lite.read_dataset(f) for f in fluids]
+    mask = h5lite.read_dataset(maskf).astype(np.int32)
+    t0 = int(h5lite.read_attributes(fluids[0], "globals")["dlbc.lb.lb.timestep"])
+    return mask, pops, t0
+
+
+def write_checkpoint(L, p, t, directory, input_lines=None, run_id="00000000T000000"):
+    """dumpCheckpoint (io/checkpoint.d:191-215): cp-fluids<i>-<sim>-<id>-t%08d.h5 for every fluid and cp-mask-... for
+    the mask under <directory>/<cpPath>, each with the `input` attribute, `metadata` and `globals/dlbc.lb.lb.timestep`,
+    so that the reference's `-r <sim>-<id>-t%08d` (or this module's) restarts from them."""
+    from . import h5lite
+    sim = P.replace_fname_tokens(p["io.simulationName"], p)
+    d = os.path.join(directory, p["io.checkpoint.cpPath"])
+    os.makedirs(d, exist_ok=True)
+    meta = metadata()
+    paths = []
+    for i in range(int(p["lb.components"])):
+        paths.append(h5lite.write_file(os.path.join(d, f"cp-fluids{i}-{sim}-{run_id}-t{t:08d}.h5"), L.get_populations(i),
+                                       input_lines=input_lines, metadata=meta, globals_={"dlbc.lb.lb.timestep": int(t)}))
+    paths.append(h5lite.write_file(os.path.join(d, f"cp-mask-{sim}-{run_id}-t{t:08d}.h5"), L.get_mask().astype(np.int32),
+                                   input_lines=input_lines, metadata=meta, globals_={"dlbc.lb.lb.timestep": int(t)}))
+    return paths
+
+
+def metadata():
+    """The `metadata` group (io/hdf5.d:290-299): revision of the code that wrote the file."""
+    return {"revisionHash": "dlbc_b200", "revisionDesc": "libdlbc_cuda (DLBC timestep on B200)", "revisionBranch": "main",
+            "revisionChanged": 0, "revisionChanges": ""}
+
+
 def _cuda_lattice(gn, C, kw, device=0, arithmetic="fast", kernel="auto"):
     from .lattice import Lattice
     return Lattice(gn, C, **kw, device=device, arithmetic=arithmetic, kernel=kernel)
 
 
-def replay(p, make_lattice=None, device_init=False, **lattice_options):
+def replay(p, make_lattice=None, device_init=False, restore=None, base_dir=".", checkpoint_dir=None, input_lines=None,
+           **lattice_options):
     """Run the case described by parameter dict `p`; returns {file-name stem: array}.
     make_lattice(gn, components, kwargs) -> object with the `Lattice` interface (default: the CUDA library).
-    device_init: generate mask and initial populations on the device instead of uploading host arrays."""
+    device_init: generate mask and initial populations on the device instead of uploading host arrays.
+    restore: name of a checkpoint to start from (the reference's `-r`), looked up relative to `base_dir`.
+    checkpoint_dir: write checkpoints there every io.checkpoint.cpFreq steps (dumpCheckpoint)."""
     gn, C, kw = lattice_kwargs(p)
     names = _fit(p["lb.fieldNames"], C, "lb.lb.fieldNames", strict=True)
     p = dict(p, **{"lb.fieldNames": names})
     blk = I.Block(gn)
-    if not device_init:
+    t_start = 0
+    if restore is not None:
+        mask0, pops0, t_start = read_checkpoint(p, restore, base_dir)
+        blk = I.Block(gn, halo=0)
+        mask, pops, device_init = mask0, pops0, False
+    elif not device_init:
         mask = initial_mask(p, blk)
         pops = initial_populations(p, blk, mask)
     L = make_lattice(gn, C, kw) if make_lattice else _cuda_lattice(gn, C, kw, **lattice_options)
@@ -252,30 +303,35 @@ def replay(p, make_lattice=None, device_init=False, **lattice_options):
                 L.set_populations(c, a, halo=blk.halo)
         if hasattr(L, "exchange_halo"):
             L.exchange_halo()  # main.d:142 (the CUDA library maintains its ghost planes itself)
-        _collect(L, p, 0, out)  # "First data dump", main.d:149
+        _collect(L, p, t_start, out)  # "First data dump", main.d:149 (after a restore: at the restored timestep)
         freqs = [p[f"lb.io.{k}Freq"] for k in ("population", "density", "colour", "velocity", "force", "mask")]
-        freqs = sorted({f for f in freqs if f > 0})
-        t, T = 0, int(p["lb.timesteps"])
+        cp_freq = int(p["io.checkpoint.cpFreq"]) if checkpoint_dir else 0
+        freqs = sorted({f for f in freqs + [cp_freq] if f > 0})
+        t, T = t_start, int(p["lb.timesteps"])
         while t < T:
             nxt = min([T] + [(t // f + 1) * f for f in freqs])  # next step at which anything is dumped
             L.step(nxt - t)
             t = nxt
             _collect(L, p, t, out)
+            if cp_freq and t % cp_freq == 0:
+                write_checkpoint(L, p, t, checkpoint_dir, input_lines)
     finally:
         if hasattr(L, "close"):
             L.close()
     return out
 
 
-def write_outputs(out, directory, run_id="00000000T000000"):
-    """Write every collected field as the reference would name it (io/io.d:157-172):
-    <field>-<sim>-<run id>-t%08d.h5 with one contiguous /OutArray dataset."""
+def write_outputs(out, directory, run_id="00000000T000000", input_lines=None):
+    """Write every collected field as the reference would name and furnish it (io/io.d:157-172, io/hdf5.d:264-299):
+    <field>-<sim>-<run id>-t%08d.h5 with one contiguous /OutArray dataset, the `input` attribute (the parameter
+    file, so that any output file can serve as input file again) and the `metadata` group."""
     from . import h5lite
     os.makedirs(directory, exist_ok=True)
     paths = []
     for k, v in out.items():
         stem, t = k.rsplit("-t", 1)
-        paths.append(h5lite.write_dataset(os.path.join(directory, f"{stem}-{run_id}-t{t}.h5"), v))
+        paths.append(h5lite.write_file(os.path.join(directory, f"{stem}-{run_id}-t{t}.h5"), v, input_lines=input_lines,
+                                       metadata=metadata() if input_lines is not None else None))
     return paths
 
 
@@ -288,15 +344,20 @@ def main(argv=None):
     ap.add_argument("--run-id", default="00000000T000000", help="time-stamp id in the file names (io/io.d:157-172)")
     ap.add_argument("--arith", default="fast", choices=["fast", "exact"])
     ap.add_argument("--device", type=int, default=0)
+    ap.add_argument("-r", "--restore", default=None, metavar="NAME",
+                    help="restart from checkpoint NAME (<outputPath>/<cpRestorePath>/cp-fluids<i>-NAME.h5, cp-mask-NAME.h5), "
+                         "as the reference's -r")
     ap.add_argument("--device-init", action="store_true",
                     help="generate mask and initial populations on the GPU (dlbc_cuda_init_*) instead of uploading them")
     a = ap.parse_args(argv)
-    p = P.parse_file(a.parameter_file, a.parameter)
-    out = replay(p, device_init=a.device_init, arithmetic=a.arith, device=a.device)
+    p = P.parse_file(a.parameter_file, a.parameter)  # (an .h5 written by DLBC or by --out works as parameter file too)
+    lines = P.read_lines(a.parameter_file)
+    out = replay(p, device_init=a.device_init, restore=a.restore, base_dir=os.path.dirname(os.path.abspath(a.parameter_file)),
+                 checkpoint_dir=a.out, input_lines=lines, arithmetic=a.arith, device=a.device)
     for k, v in out.items():
         print(f"{k}: shape {v.shape}, sum {float(np.sum(v)):.15g}")
     if a.out:
-        write_outputs(out, a.out, a.run_id)
+        write_outputs(out, a.out, a.run_id, input_lines=lines)
 
 
 if __name__ == "__main__":

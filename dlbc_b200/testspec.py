@@ -75,7 +75,7 @@ class TestSpec:
         for c in cmp_.get("comparison", []):
             if c.get("type") != "h5diff":
                 raise SpecError(f"Unknown comparison type '{c.get('type')}'.")  # compare.py:86
-            m = re.search(r"t(\d{8})\.h5$", c["files"])
+            m = re.search(r"t(\d{8})\.h5$", c["files"])  # ("%data%-<sim>*-t00000005.h5")
             if not m:
                 raise SpecError(f"cannot find the timestep in the file pattern '{c['files']}'")
             acc = float(c["accuracy"]) if "accuracy" in c else None
@@ -90,6 +90,8 @@ class TestSpec:
         `floor` > 0 replaces them (a GPU run is "another compiler": the reference itself relaxes such comparisons).
         Returns [(data, time, max abs difference, bound)]; raises AssertionError on the first violation."""
         p = P.parse_file(os.path.join(self.root, self.input_file), self.overrides(mode) + list(subtest))
+        if self.checkpoint:  # run.py: `-r <name>`; the restore path is relative to the test's directory
+            replay_options = dict(replay_options, restore=self.checkpoint["name"], base_dir=self.root)
         out = R.replay(p, make_lattice=make_lattice, **replay_options)
         sim = P.replace_fname_tokens(p["io.simulationName"], p)
         report = []

@@ -66,6 +66,12 @@ def main():
             out[f"density-{c}-t{t}"] = g(f"lb/bdist2-3d/reference-data/density-{c}-*t{t:08d}.h5")
     codec.save(os.path.join(HERE, "bdist2-3d.npz"), **out)
 
+    # --- technical/checkpoint-3d: its parameter file exists only as the `input` attribute of the output files
+    # (the test's input file IS reference-data/colour-red-blue-checkpoint-3d-t00000000.h5): extracted to in/
+    from dlbc_b200 import h5lite as _h5
+    _lines = _h5.read_attributes(os.path.join(REF, "technical/checkpoint-3d/reference-data/colour-red-blue-checkpoint-3d-t00000000.h5"))["input"]
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "in", "checkpoint-3d.in"), "w") as _f:
+        _f.write("\n".join(_lines) + "\n")
     # --- technical/checkpoint-3d: restart KAT (checkpoint populations + mask -> 5 steps)
     out = {}
     R = "technical/checkpoint-3d/reference-data/"

@@ -179,6 +179,91 @@ def test_spec_driven_replay_on_the_gpu(golden, case):
     assert any(t == 10 for _, t, _, _ in rep) and all(d == 0.0 for _, t, d, _ in rep if t == 0)
 
 
+# ---- technical/checkpoint-3d: the input file is an .h5, the state comes from a checkpoint (-r) ----------------
+def _checkpoint_test_dir(tmp_path, g):
+    """The reference's test directory rebuilt from the fixtures with THIS repo's HDF5 writer: reference-data/<output
+    file with the `input` attribute> and reference-data/cp/cp-{fluids0,fluids1,mask}-checkpoint-3d-t00000000.h5 with
+    `globals/dlbc.lb.lb.timestep`."""
+    import shutil
+    from dlbc_b200 import h5lite as H
+    lines = P.read_lines(os.path.join(IN, "checkpoint-3d.in"))
+    rd = tmp_path / "reference-data"
+    (rd / "cp").mkdir(parents=True)
+    H.write_file(str(rd / "colour-red-blue-checkpoint-3d-t00000000.h5"), g["colour-red-blue-t0"], input_lines=lines,
+                 metadata=R.metadata())
+    for name, key in (("cp-fluids0", "cp-fluids0-t0"), ("cp-fluids1", "cp-fluids1-t0"), ("cp-mask", "cp-mask-t0")):
+        H.write_file(str(rd / "cp" / f"{name}-checkpoint-3d-t00000000.h5"), g[key], input_lines=lines, metadata=R.metadata(),
+                     globals_={"dlbc.lb.lb.timestep": 0})
+    shutil.copy(os.path.join(IN, "checkpoint-3d.json"), tmp_path / "checkpoint-3d.json")
+    return str(tmp_path / "checkpoint-3d.json")
+
+
+def test_h5_attributes_roundtrip(tmp_path):
+    from dlbc_b200 import h5lite as H
+    lines = P.read_lines(os.path.join(IN, "checkpoint-3d.in"))
+    a = np.arange(2 * 3 * 4 * 19, dtype=np.float64).reshape(2, 3, 4, 19)
+    f = str(tmp_path / "x.h5")
+    H.write_file(f, a, input_lines=lines, metadata=R.metadata(), globals_={"dlbc.lb.lb.timestep": 12345})
+    assert H.list_root(f) == ["OutArray", "globals", "metadata"]
+    assert_bitexact(H.read_dataset(f), a)
+    assert H.read_attributes(f)["input"] == lines
+    assert H.read_attributes(f, "globals") == {"dlbc.lb.lb.timestep": 12345}
+    assert H.read_attributes(f, "metadata")["revisionChanged"] == 0 and H.read_attributes(f, "metadata")["revisionBranch"] == ["main"]
+    p = P.parse_file(f)  # an output file serves as parameter file (parameters.d:172-174)
+    assert p["lattice.gn"] == [16, 16, 16] and p["io.checkpoint.cpRestorePath"] == "../reference-data/cp"
+
+
+REF_CP = "/root/reference/tests/runnable/tests/technical/checkpoint-3d"
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_CP), reason="the reference tree only exists in the build container")
+def test_attribute_reader_on_the_reference_files_and_spec_from_the_reference_tree(golden):
+    """libhdf5-written files: `input`, `metadata`, `globals`; and the reference's own checkpoint-3d test directory
+    replayed as it stands (input file .h5, restore from reference-data/cp) on the oracle."""
+    from dlbc_b200 import h5lite as H
+    from dlbc_b200.testspec import TestSpec
+    f = os.path.join(REF_CP, "reference-data", "cp", "cp-fluids0-checkpoint-3d-t00000000.h5")
+    assert H.read_attributes(f, "globals") == {"dlbc.lb.lb.timestep": 0}
+    assert H.read_attributes(f, "metadata")["revisionBranch"] == ["master"]
+    assert "checkpoint.cpKeep = 2" in H.read_attributes(f)["input"]  # (this checkpoint stems from another run of the test)
+    f = os.path.join(REF_CP, "reference-data", "colour-red-blue-checkpoint-3d-t00000000.h5")
+    assert H.read_attributes(f)["input"] == P.read_lines(os.path.join(IN, "checkpoint-3d.in"))
+    rep = TestSpec(os.path.join(REF_CP, "checkpoint-3d.json")).run(golden("checkpoint-3d"), "full", make_lattice=_oracle_lattice,
+                                                                   floor=1e-15)
+    assert {t for _, t, _, _ in rep} == {0, 5} and all(d == 0.0 for _, t, d, _ in rep if t == 0)
+
+
+def test_checkpoint_3d_spec_on_the_oracle(golden, tmp_path):
+    from dlbc_b200.testspec import TestSpec
+    spec = _checkpoint_test_dir(tmp_path, golden("checkpoint-3d"))
+    rep = TestSpec(spec).run(golden("checkpoint-3d"), "full", make_lattice=_oracle_lattice, floor=1e-15)
+    assert {t for _, t, _, _ in rep} == {0, 5} and all(d == 0.0 for _, t, d, _ in rep if t == 0)
+
+
+@pytest.mark.gpu
+def test_checkpoint_3d_spec_on_the_gpu_and_checkpoints_written_by_it(golden, tmp_path):
+    """technical/checkpoint-3d through libdlbc_cuda: input from an .h5, state from cp files, outputs at t = 0 and 5;
+    then the checkpoint IT writes at t = 5 (cpFreq = 5) restarts a second run whose t = 5 dump equals the first's."""
+    from dlbc_b200 import h5lite as H
+    from dlbc_b200.testspec import TestSpec
+    g = golden("checkpoint-3d")
+    spec = _checkpoint_test_dir(tmp_path, g)
+    rep = TestSpec(spec).run(g, "full", arithmetic="exact", floor=1e-15)
+    assert {t for _, t, _, _ in rep} == {0, 5}
+    inp = str(tmp_path / "reference-data" / "colour-red-blue-checkpoint-3d-t00000000.h5")
+    p = P.parse_file(inp)
+    out1 = R.replay(p, restore="checkpoint-3d-t00000000", base_dir=str(tmp_path), checkpoint_dir=str(tmp_path / "output"),
+                    input_lines=P.read_lines(inp), arithmetic="exact")
+    cp = tmp_path / "output" / "cp"
+    assert sorted(os.listdir(cp)) == [f"cp-{n}-checkpoint-3d-00000000T000000-t00000005.h5" for n in ("fluids0", "fluids1", "mask")]
+    assert H.read_attributes(str(cp / "cp-fluids0-checkpoint-3d-00000000T000000-t00000005.h5"), "globals") == {"dlbc.lb.lb.timestep": 5}
+    assert_close(H.read_dataset(str(cp / "cp-fluids1-checkpoint-3d-00000000T000000-t00000005.h5")), g["cp-fluids1-t5"], what="cp t5")
+    p2 = dict(p, **{"io.checkpoint.cpRestorePath": "cp"})
+    out2 = R.replay(p2, restore="checkpoint-3d-00000000T000000-t00000005", base_dir=str(tmp_path), arithmetic="exact")
+    for k in out2:
+        assert k.endswith("t00000005") and np.array_equal(out2[k], out1[k]), k
+
+
 # ---- replay: GPU ------------------------------------------------------------------------------------
 @pytest.mark.gpu
 @pytest.mark.parametrize("case,times", [("merging-droplets-3d", (0, 10)), ("bdist2-3d", (0, 10)),
