@@ -422,13 +422,20 @@ def run_ours(args, rank, world, local_rank):
         if os.path.exists(tp):
             try:
                 with open(tp) as f:
-                    tr = json.load(f).get(dom)
-                    if tr and not porous:  # ncu-measured DRAM bytes per site of this kernel x the sites of one launch
-                        roof["traffic"] = tr["bytes_per_site"] * sites_local
-                        roof["traffic_bytes_per_site"] = tr["bytes_per_site"]
-                        roof["traffic_source"] = tr["source"]
+                    table = json.load(f)
+                # ncu-measured DRAM bytes per site of THIS kernel instantiation (component count / mask) x the sites
+                # of one launch; captured once per round on a 512x512x128 (256^3 for C = 1) launch, not in this run
+                key = dom + ("/porous" if porous else "/c1" if ncomp == 1 else "")
+                tr = table.get(key)
+                if tr and ncomp <= 2:
+                    roof["traffic"] = tr["bytes_per_site"] * sites_local
+                    roof["traffic_bytes_per_site"] = tr["bytes_per_site"]
+                    roof["traffic_source"] = tr["source"]
             except Exception:
                 pass
+        if len(acc) > 1:
+            roof["note"] = ("frac is the dominant kernel's alone; the step also runs " +
+                            ", ".join(k for k in acc if k != dom) + ": see step_frac")
     else:
         achieved = b_alg * sites_local / (ms / args.steps * 1e-3) * 1e-9
         roof = {"bound": "hbm", "kernel": "whole step (per GPU)", "achieved": achieved, "peak": peak, "unit": "GB/s",

@@ -42,10 +42,15 @@ import dlbc.mpi;
 @("param") int arithmetic = 0;
 /// 0 = let the library choose the kernel variant.
 @("param") int kernelVariant = 0;
+/// Generate mask and initial populations on the device (dlbc_cuda_init_*) instead of uploading L.mask / L.fluids:
+/// for lattices whose state should never exist on the host.  Supported: maskInit None/Box/Tube/Plates/Walls and
+/// fluidInit EqDist, EqDistRandom, EqDistPerturb(Frac), EqDistSphere(Frac), EqDistTwoSpheres(Frac),
+/// EqDistCylinder(Frac); the draws are those of THIS rank's block, as lb/init.d:109-125 makes them.
+@("param") bool deviceInit = false;
 
 // ---- extern(C) binding of include/dlbc_cuda.h (same style as src/dlbc/mpi.d:16-18) ----------------
 @trusted nothrow @nogc extern(C) {
-  enum DLBC_CUDA_ABI_VERSION = 1;
+  enum DLBC_CUDA_ABI_VERSION = 3;
   enum DLBC_CUDA_MAX_COMPONENTS = 4;
   enum DLBC_CUDA_NCCL_ID_BYTES = 128;
 
@@ -81,6 +86,22 @@ import dlbc.mpi;
   int dlbc_cuda_step(dlbc_cuda_ctx* ctx, int nsteps);
   int dlbc_cuda_sync(dlbc_cuda_ctx* ctx);
   int dlbc_cuda_total_mass(dlbc_cuda_ctx* ctx, int comp, double* result);
+  int dlbc_cuda_download_density(dlbc_cuda_ctx* ctx, int comp, double* result, int halo);
+  int dlbc_cuda_download_colour(dlbc_cuda_ctx* ctx, int comp1, int comp2, double* result, int halo);
+  int dlbc_cuda_download_velocity(dlbc_cuda_ctx* ctx, int comp, double* result, int halo);
+  int dlbc_cuda_download_force(dlbc_cuda_ctx* ctx, int comp, double* result, int halo);
+  int dlbc_cuda_download_pressure(dlbc_cuda_ctx* ctx, double* result, int halo);
+  int dlbc_cuda_download_corrected_velocity(dlbc_cuda_ctx* ctx, int comp, double* result, int halo);
+  int dlbc_cuda_volume_averaged_density(dlbc_cuda_ctx* ctx, const(long)* offset, int halfWidth, double* result);
+  // geometry / initial conditions generated on the device (lb/mask.d:134-172, fields/init.d:52-82,84-313,469-477)
+  enum { DLBC_MASK_NONE, DLBC_MASK_BOX, DLBC_MASK_TUBE, DLBC_MASK_PLATES, DLBC_MASK_WALLS }  // = enum MaskInit order minus File
+  enum { DLBC_INIT_EQDIST, DLBC_INIT_EQDIST_RANDOM, DLBC_INIT_EQDIST_PERTURB, DLBC_INIT_EQDIST_PERTURB_FRAC }
+  int dlbc_cuda_init_mask(dlbc_cuda_ctx* ctx, int kind, int axis, int wallOffset, int thickness, const(int)* hasWall);
+  int dlbc_cuda_init_populations(dlbc_cuda_ctx* ctx, int comp, int kind, double density, double perturb, uint seed, long skip);
+  int dlbc_cuda_init_spheres(dlbc_cuda_ctx* ctx, int comp, int ncentres, const(double)* centres, int skipAxis,
+                             double radius, double thickness, double density1, double density2);
+  int dlbc_cuda_init_axis_profile(dlbc_cuda_ctx* ctx, int comp, int axis, const(double)* values);
+  int dlbc_cuda_init_wall(dlbc_cuda_ctx* ctx);
 }
 
 private __gshared dlbc_cuda_ctx* ctx;
