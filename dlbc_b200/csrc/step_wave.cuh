@@ -172,10 +172,13 @@ wave_kernel(Geom g, Fields fl, StepParams P, Wave w) {
       __syncthreads();  // all psi stores of the block precede (CTA scope) the lead thread's release below
       if (lead) red_release_add(w.sync + wi.cnt + wi.zg * (w.tyb + 2) + wi.row, 1);
     } else if (wi.kind == 2) {
-      if (threadIdx.x < 9) {
-        const int *c = wave_wait_counter(g, w, wi, threadIdx.x);
-        if (c) wave_poll_until(c, w.xb * w.nsub, 32);
-        wave_acquire();
+      if (threadIdx.x < 32) {
+        if (threadIdx.x < 9) {
+          const int *c = wave_wait_counter(g, w, wi, threadIdx.x);
+          if (c) wave_poll_until(c, w.xb * w.nsub, 32);
+        }
+        __syncwarp();    // the polling lanes leave their loops one by one: ONE converged fence for the warp instead
+        wave_acquire();  // of one per straggler (1.56 fences per item measured); the warp barrier orders every poll before it
       }
       __syncthreads();
       if (x < g.nx) fused_site<C, EQ, true, MASK, EXACT, true, POL_STREAM>(g, fl, P, x, wi.y, wi.zg);
