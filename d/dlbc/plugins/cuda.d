@@ -86,6 +86,9 @@ import dlbc.mpi;
   int dlbc_cuda_step(dlbc_cuda_ctx* ctx, int nsteps);
   int dlbc_cuda_sync(dlbc_cuda_ctx* ctx);
   int dlbc_cuda_total_mass(dlbc_cuda_ctx* ctx, int comp, double* result);
+  // no counterpart in the reference: allocation-free, context-free sums from device pointers
+  int dlbc_cuda_mass_momentum_no_alloc(int ncomp, long nx, long ny, long nz, const(double)* dPops, const(ubyte)* dMask,
+                                       double* dOut, void* stream, char* err, size_t errCap);
   int dlbc_cuda_download_density(dlbc_cuda_ctx* ctx, int comp, double* result, int halo);
   int dlbc_cuda_download_colour(dlbc_cuda_ctx* ctx, int comp1, int comp2, double* result, int halo);
   int dlbc_cuda_download_velocity(dlbc_cuda_ctx* ctx, int comp, double* result, int halo);

@@ -33,6 +33,7 @@ SYMBOLS = [
     "dlbc_cuda_set_option", "dlbc_cuda_download_pressure", "dlbc_cuda_download_corrected_velocity",
     "dlbc_cuda_volume_averaged_density", "dlbc_cuda_init_mask", "dlbc_cuda_init_populations", "dlbc_cuda_init_wall",
     "dlbc_cuda_init_spheres", "dlbc_cuda_init_axis_profile", "dlbc_cuda_site_function",
+    "dlbc_cuda_mass_momentum_no_alloc",
 ]
 MASK_KIND = {"None": 0, "Box": 1, "Tube": 2, "Plates": 3, "Walls": 4}
 INIT_KIND = {"EqDist": 0, "EqDistRandom": 1, "EqDistPerturb": 2, "EqDistPerturbFrac": 3}
@@ -110,6 +111,9 @@ def load():
     L.dlbc_cuda_init_spheres.argtypes = [vp, C.c_int, C.c_int, dp, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double]
     L.dlbc_cuda_init_axis_profile.argtypes = [vp, C.c_int, C.c_int, dp]
     L.dlbc_cuda_site_function.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, dp, dp, dp]
+    # device pointers as integers (tensor.data_ptr()); stream handle; message buffer
+    L.dlbc_cuda_mass_momentum_no_alloc.argtypes = [C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
+                                                   C.c_void_p, C.c_void_p, C.c_char_p, C.c_size_t]
     for name in SYMBOLS:
         fn = getattr(L, name)
         if name not in ("dlbc_cuda_last_error", "dlbc_cuda_timestep"):

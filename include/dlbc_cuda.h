@@ -183,6 +183,26 @@ int dlbc_cuda_volume_averaged_density(dlbc_cuda_ctx *ctx, const int64_t offset[3
  * sequential order, so equal only to summation round-off). */
 int dlbc_cuda_total_mass(dlbc_cuda_ctx *ctx, int comp, double *out);
 int dlbc_cuda_total_momentum(dlbc_cuda_ctx *ctx, int comp, double out[3]);
+/* mass_momentum_no_alloc: NO COUNTERPART IN THE REFERENCE -- added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  The same sums as total_mass / total_momentum (same kernels' grid and tree order: bit-identical to a
+ * single-rank context on the same data), but context-free and allocation-free: the call performs no cudaMalloc,
+ * cudaFree or any other allocating routine; it enqueues two kernels on `stream` (a cudaStream_t, NULL = the
+ * default stream) of the CURRENT device and returns without synchronising.  All pointers are DEVICE pointers:
+ *   d_pops[ncomp][19][nz][ny][nx]  populations, x fastest, directions in connectivity.d order
+ *   d_mask[nz][ny][nx]             uint8, nonzero = not a fluid site (skipped); NULL = every site is fluid
+ *   d_out[ncomp][4]                mass, momentum x, y, z of every component
+ * The per-block partial sums live in one file-scope __device__ array of DLBC_CUDA_NO_ALLOC_SCRATCH_BYTES
+ * (csrc/no_alloc.cu) that every GPU loading the library holds until the process exits.  Limits: ncomp <=
+ * DLBC_CUDA_NO_ALLOC_MAX_COMPONENTS and nx * ny * nz <= DLBC_CUDA_NO_ALLOC_MAX_SITES; larger sizes are rejected
+ * (non-zero return, message in err[0..err_cap), which may be NULL).  Every call on a device shares the array and
+ * it keeps the last call's contents (nothing needs clearing: each call overwrites every partial it reads), so
+ * two calls whose kernels can OVERLAP on the GPU (different streams without a dependency) RACE: serialise them. */
+#define DLBC_CUDA_NO_ALLOC_MAX_COMPONENTS 4
+#define DLBC_CUDA_NO_ALLOC_MAX_SITES ((int64_t)1 << 31)
+#define DLBC_CUDA_NO_ALLOC_SCRATCH_BYTES (DLBC_CUDA_NO_ALLOC_MAX_COMPONENTS * 4 * 1184 * 8) /* 151552 */
+int dlbc_cuda_mass_momentum_no_alloc(int ncomp, int64_t nx, int64_t ny, int64_t nz, const double *d_pops,
+                                     const uint8_t *d_mask, double *d_out, void *stream, char *err, size_t err_cap);
 
 /* ---- introspection / measurement --------------------------------------------------------------
  * tables: the device's copy of connectivity.d:401-418 / :198-212 / :253-257 (velocities[19][3],
