@@ -157,12 +157,14 @@ __device__ __forceinline__ void store_pop(double *a, double v, uint64_t pol) {
 // (advectable) site: f[q] = bounce-back(mask[p - c_q]) ? old[p][bounce q] : old[p - c_q][q].
 // ps = f_plane(f_old, g, zg, c) + n.sxy  (per-thread pointer to the site's q = 0 entry: every
 // access is then ps[int offset], one IMAD.WIDE), ms = mask_plane(mask, g, zg) + n.sxy.
-template <bool MASK, int POL = POL_DEFAULT>
+// SELF (with MASK): a solid site reads its OWN populations, direction for direction (see pull19_bits).
+template <bool MASK, int POL = POL_DEFAULT, bool SELF = false>
 __device__ __forceinline__ void pull19(const double *__restrict__ ps, const uint8_t *__restrict__ ms, const Geom &g,
                                        const Nbr &n, double (&f)[Q]) {
   const uint64_t pol = make_policy<POL>();
   if (POL == POL_DEFAULT) {
     // stand-alone kernels: the compiler's own address arithmetic measured faster there
+    const bool self = MASK && SELF && ms[0] != 0;
 #pragma unroll
     for (int q = 0; q < Q; q++) {
       const int d = n.ox[1 - cx(q)] + n.oy[1 - cy(q)];  // in-plane offset to the upstream site p - c_q
@@ -170,6 +172,7 @@ __device__ __forceinline__ void pull19(const double *__restrict__ ps, const uint
       if (MASK && q > 0) {
         if (ms[d - cz(q) * g.plane]) src = qslot(bounce(q)) * g.plane;
       }
+      if (self) src = qslot(q) * g.plane;
       f[q] = load_pop<POL>(ps + src, pol);
     }
   } else {
@@ -190,7 +193,9 @@ __device__ __forceinline__ void pull19(const double *__restrict__ ps, const uint
 // instead of 18 byte loads per component whose results steer the addresses of the population loads:
 // one 4-byte load per site serves every component, the streaming step and the force (geometry is static,
 // the bits are built once at mask upload).  bounce-back of direction q looks at p - c_q, i.e. bit bounce(q).
-template <int POL = POL_DEFAULT>
+// SELF: a solid site (bit 0) reads its OWN populations, direction for direction, so that the caller can carry them
+// along to the new buffer (fused_site) -- an address select, not a branch.
+template <int POL = POL_DEFAULT, bool SELF = false>
 __device__ __forceinline__ void pull19_bits(const double *__restrict__ ps, uint32_t bits, const Geom &g, const Nbr &n,
                                             double (&f)[Q]) {
   const uint64_t pol = make_policy<POL>();
@@ -199,6 +204,7 @@ __device__ __forceinline__ void pull19_bits(const double *__restrict__ ps, uint3
     const int d = n.ox[1 - cx(q)] + n.oy[1 - cy(q)];
     int src = qslot(q) * g.plane - cz(q) * g.fz + d;
     if (q > 0 && ((bits >> bounce(q)) & 1u)) src = qslot(bounce(q)) * g.plane;
+    if (SELF && (bits & 1u)) src = qslot(q) * g.plane;
     if (POL == POL_DEFAULT) f[q] = load_pop<POL>(ps + src, pol);
     else f[q] = load_pop<POL>(ptr_at(ps, src), pol);
   }

@@ -209,25 +209,31 @@ __device__ __forceinline__ void bdist2_relax_fast(double (&f)[Q], const double (
 // lb/collision.d:100-116: dv, equilibrium, BGK relaxation of one component at one site.
 // F = Shan-Chen force on this component (force.d), m = raw momentum of f, u = BDist2 common
 // velocity (collision.d:156-196; ignored otherwise).
-template <int EQ, bool EXACT>
+// keep (only looked at when KEEP): this lane's site does not collide (a solid site whose populations are carried
+// along so that whole sectors are written, step_two_pass.cuh): relax with omega = 0 towards the finite
+// equilibrium of rho = 1, dv = 0 -- f * 1 + 0 * eq -- which returns every f[q] bit for bit (a -0.0 would come back
+// as +0.0; populations are sums of non-negative terms) without a second code path for the warp to diverge into.
+template <int EQ, bool EXACT, bool KEEP = false>
 __device__ __forceinline__ void collide_site(double (&f)[Q], double rho, const double (&m)[3],
                                              const double (&F)[3], const double (&u)[3],
-                                             const StepParams &P, int c) {
+                                             const StepParams &P, int c, bool keep = false) {
   double dv[3];
+  if (KEEP && keep) rho = 1.0;
   const double inv_rho = EXACT ? 0.0 : 1.0 / rho;
 #pragma unroll
   for (int d = 0; d < 3; d++) {
     dv[d] = P.tau[c] * (P.gacc[d] + div_by<EXACT>(F[d], rho, inv_rho));
     if (EQ == 2) dv[d] += u[d];
+    if (KEEP && keep) dv[d] = 0.0;
   }
+  const double omega = (KEEP && keep) ? 0.0 : P.omega[c], om1 = (KEEP && keep) ? 1.0 : P.one_minus_omega[c];
   if (EQ == 2 && !EXACT) {
-    bdist2_relax_fast(f, dv, rho, P.omega[c], P.one_minus_omega[c]);
+    bdist2_relax_fast(f, dv, rho, omega, om1);
     return;
   }
   double eq[Q];
   if (EQ == 2) eqdist_bdist2(dv, rho, eq);
   else eqdist_poly<EQ, EXACT>(m, dv, rho, eq);
-  const double omega = P.omega[c], om1 = P.one_minus_omega[c];
 #pragma unroll
   for (int q = 0; q < Q; q++) f[q] = f[q] * om1 + omega * eq[q];
 }

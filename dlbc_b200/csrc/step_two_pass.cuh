@@ -17,6 +17,9 @@
 #pragma once
 #include "lattice.cuh"
 
+#ifndef DLBC_SOLID_COPY
+#define DLBC_SOLID_COPY 1  // 1: the step kernels carry the populations of solid sites along (see fused_site)
+#endif
 #ifndef DLBC_MASK_BLOCKS
 #define DLBC_MASK_BLOCKS 3  // resident 128-thread blocks per SM of the MASK instantiations
 #endif
@@ -27,11 +30,11 @@ namespace dlbc {
 // Mask-aware gather.  The wave variant (POL != POL_DEFAULT) steers bounce-back from the neighbourhood bits
 // (porous 512^3: 4.53 -> 4.82 GLUPS); the stand-alone kernels measured 6 % slower with the bits than with
 // the mask bytes (fused 21.7 -> 23.0 ms), so they keep the bytes.
-template <bool MASK, int POL>
+template <bool MASK, int POL, bool SELF = false>
 __device__ __forceinline__ void pull_site(const double *__restrict__ ps, const uint8_t *__restrict__ ms, uint32_t bits,
                                           const Geom &g, const Nbr &n, double (&f)[Q]) {
-  if (MASK && POL != POL_DEFAULT) pull19_bits<POL>(ps, bits, g, n, f);
-  else pull19<MASK, POL>(ps, ms, g, n, f);
+  if (MASK && POL != POL_DEFAULT) pull19_bits<POL, SELF>(ps, bits, g, n, f);
+  else pull19<MASK, POL, SELF>(ps, ms, g, n, f);
 }
 
 // site's neighbourhood bits: from Fields::nb in the wave variant, else just the own-site flag from the bytes
@@ -50,7 +53,21 @@ __device__ __forceinline__ void psi_site(const Geom &g, const Fields &fl, int x,
   const Nbr n = make_nbr(g, x, y);
   const uint8_t *ms = mask_plane(fl.mask, g, zg) + n.sxy;
   const uint32_t bits = site_bits<MASK, POL>(g, fl, zg, n);
-  if (MASK && (bits & 1u)) return;  // psi of solid sites is never read (force.d:273 uses the own-site psi)
+  // psi of solid sites is never read (force.d:273 uses the own-site psi)
+  if (MASK && (bits & 1u)) {
+    if (DLBC_SOLID_COPY) {
+      // ... but written all the same (0.0, no loads): the warp's stores then cover whole 32-byte sectors
+#pragma unroll
+      for (int c = 0; c < C; c++) {
+        psi_plane(fl.psi, g, zg, c)[n.sxy] = 0.0;
+        if (g.periodic_z_local) {
+          if (zg == g.nz) psi_plane(fl.psi, g, 0, c)[n.sxy] = 0.0;
+          if (zg == 1) psi_plane(fl.psi, g, g.nz + 1, c)[n.sxy] = 0.0;
+        }
+      }
+    }
+    return;
+  }
   const double *ps = f_plane(fl.f_old, g, zg, 0) + n.sxy;
   double v[C];
   if (BATCH) {
@@ -195,17 +212,23 @@ __device__ __forceinline__ void fused_site(const Geom &g, const Fields &fl, cons
   const uint8_t *ms = mask_plane(fl.mask, g, zg) + n.sxy;
   const uint32_t bits = site_bits<MASK, POL>(g, fl, zg, n);
   // Solid sites: advection copies them (advection.d:83-85) and they never collide; both population buffers hold
-  // their (static) values since upload, so there is nothing to do.  (The fluid sites of a warp then write 32-byte
-  // sectors only in part, which the L2 has to fill from DRAM first: 23.2 GB read per 33.5 M sites on the porous
-  // workload against 12.1 GB without a mask.  Writing the solid sites' values back as well removes the fill
-  // reads but costs 38 loads + 38 stores per solid thread: measured 10 % SLOWER, profiles/README.md.)
-  if (MASK && (bits & 1u)) return;
+  // their (static) values since upload, so there is nothing to do -- except that the fluid sites of a warp then
+  // write 32-byte sectors only in part, which the L2 has to fill from DRAM first (porous workload, 30 % solid:
+  // 23.1 GB read per 33.5 M sites against 12.1 GB without a mask, profiles/r02/r02d_porous_*).  CARRY: the
+  // solid lanes go through the same instructions as their fluid neighbours -- they gather their OWN populations
+  // (an address select in pull19*), collide with omega = 0 (collide_site KEEP: f comes back bit for bit) and
+  // store them, so every sector is written whole: porous 512^3 4.80 -> 5.59 GLUPS (single launch: reads 23.1 ->
+  // 13.4 GB, r02e_porous_*), 4.30 -> 4.71 GLUPS (two kernels).  (A separate copy branch for
+  // the solid lanes -- the warp runs both paths one after the other -- measured 10 % SLOWER than not writing.)
+  constexpr bool CARRY = MASK && DLBC_SOLID_COPY;
+  const bool solid = MASK && (bits & 1u);
+  if (solid && !CARRY) return;
 
   double f[C][Q], rho[C], m[C][3], F[C][3];
   const double *ps = f_plane(fl.f_old, g, zg, 0) + n.sxy;
 #pragma unroll
   for (int c = 0; c < C; c++) {
-    pull_site<MASK, POL>(ps + c * g.fc, ms, bits, g, n, f[c]);
+    pull_site<MASK, POL, CARRY>(ps + c * g.fc, ms, bits, g, n, f[c]);
     rho[c] = density19(f[c]);
     momentum19(f[c], m[c]);
     F[c][0] = 0.0; F[c][1] = 0.0; F[c][2] = 0.0;
@@ -224,7 +247,7 @@ __device__ __forceinline__ void fused_site(const Geom &g, const Fields &fl, cons
   if (EQ == 2) common_velocity<C, EXACT>(P, m, rho, u);
 #pragma unroll
   for (int c = 0; c < C; c++) {
-    collide_site<EQ, EXACT>(f[c], rho[c], m[c], F[c], u, P, c);
+    collide_site<EQ, EXACT, CARRY>(f[c], rho[c], m[c], F[c], u, P, c, solid);
     store19<POL>(g, fl.f_new, zg, c, n.sxy, f[c]);
   }
 }
