@@ -21,7 +21,10 @@
 #define DLBC_SOLID_COPY 1  // 1: the step kernels carry the populations of solid sites along (see fused_site)
 #endif
 #ifndef DLBC_MASK_BLOCKS
-#define DLBC_MASK_BLOCKS 3  // resident 128-thread blocks per SM of the MASK instantiations
+#define DLBC_MASK_BLOCKS 3  // resident 128-thread blocks per SM of the MASK instantiations: stand-alone fused kernel
+#endif
+#ifndef DLBC_MASK_BLOCKS_WAVE
+#define DLBC_MASK_BLOCKS_WAVE 3  // ... and single-launch kernel
 #endif
 namespace dlbc {
 
@@ -206,11 +209,16 @@ __device__ __forceinline__ void store19(const Geom &g, double *__restrict__ f_ne
   }
 }
 
-template <int C, int EQ, bool SC, bool MASK, bool EXACT, bool COHERENT = false, int POL = POL_DEFAULT>
-__device__ __forceinline__ void fused_site(const Geom &g, const Fields &fl, const StepParams &P, int x, int y, int zg) {
-  const Nbr n = make_nbr(g, x, y);
+// One site of K2 in two halves, so that a caller can put a wait between the gather of the populations (which
+// depend on nothing written in this launch) and the rest (step_wave.cuh waits for psi there):
+//   fused_gather: f[c][q] <- streamed populations; returns false when there is nothing to do for this site
+//   fused_finish: moments, Shan-Chen force from psi, collision, store
+template <int C, bool MASK, int POL = POL_DEFAULT>
+__device__ __forceinline__ bool fused_gather(const Geom &g, const Fields &fl, int x, int y, int zg, Nbr &n, uint32_t &bits,
+                                             double (&f)[C][Q]) {
+  n = make_nbr(g, x, y);
   const uint8_t *ms = mask_plane(fl.mask, g, zg) + n.sxy;
-  const uint32_t bits = site_bits<MASK, POL>(g, fl, zg, n);
+  bits = site_bits<MASK, POL>(g, fl, zg, n);
   // Solid sites: advection copies them (advection.d:83-85) and they never collide; both population buffers hold
   // their (static) values since upload, so there is nothing to do -- except that the fluid sites of a warp then
   // write 32-byte sectors only in part, which the L2 has to fill from DRAM first (porous workload, 30 % solid:
@@ -221,14 +229,21 @@ __device__ __forceinline__ void fused_site(const Geom &g, const Fields &fl, cons
   // 13.4 GB, r02e_porous_*), 4.30 -> 4.71 GLUPS (two kernels).  (A separate copy branch for
   // the solid lanes -- the warp runs both paths one after the other -- measured 10 % SLOWER than not writing.)
   constexpr bool CARRY = MASK && DLBC_SOLID_COPY;
-  const bool solid = MASK && (bits & 1u);
-  if (solid && !CARRY) return;
-
-  double f[C][Q], rho[C], m[C][3], F[C][3];
+  if (MASK && (bits & 1u) && !CARRY) return false;
   const double *ps = f_plane(fl.f_old, g, zg, 0) + n.sxy;
 #pragma unroll
+  for (int c = 0; c < C; c++) pull_site<MASK, POL, CARRY>(ps + c * g.fc, ms, bits, g, n, f[c]);
+  return true;
+}
+
+template <int C, int EQ, bool SC, bool MASK, bool EXACT, bool COHERENT = false, int POL = POL_DEFAULT>
+__device__ __forceinline__ void fused_finish(const Geom &g, const Fields &fl, const StepParams &P, int zg, const Nbr &n,
+                                             uint32_t bits, double (&f)[C][Q]) {
+  constexpr bool CARRY = MASK && DLBC_SOLID_COPY;
+  const bool solid = MASK && (bits & 1u);
+  double rho[C], m[C][3], F[C][3];
+#pragma unroll
   for (int c = 0; c < C; c++) {
-    pull_site<MASK, POL, CARRY>(ps + c * g.fc, ms, bits, g, n, f[c]);
     rho[c] = density19(f[c]);
     momentum19(f[c], m[c]);
     F[c][0] = 0.0; F[c][1] = 0.0; F[c][2] = 0.0;
@@ -250,6 +265,15 @@ __device__ __forceinline__ void fused_site(const Geom &g, const Fields &fl, cons
     collide_site<EQ, EXACT, CARRY>(f[c], rho[c], m[c], F[c], u, P, c, solid);
     store19<POL>(g, fl.f_new, zg, c, n.sxy, f[c]);
   }
+}
+
+template <int C, int EQ, bool SC, bool MASK, bool EXACT, bool COHERENT = false, int POL = POL_DEFAULT>
+__device__ __forceinline__ void fused_site(const Geom &g, const Fields &fl, const StepParams &P, int x, int y, int zg) {
+  Nbr n;
+  uint32_t bits;
+  double f[C][Q];
+  if (fused_gather<C, MASK, POL>(g, fl, x, y, zg, n, bits, f))
+    fused_finish<C, EQ, SC, MASK, EXACT, COHERENT, POL>(g, fl, P, zg, n, bits, f);
 }
 
 template <int C, int EQ, bool SC, bool MASK, bool EXACT>

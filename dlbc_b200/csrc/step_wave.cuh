@@ -145,6 +145,9 @@ __device__ __forceinline__ void red_release_add(int *p, int v) {
   asm volatile("red.release.gpu.global.add.s32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
 }
 
+#ifndef DLBC_WAVE_EARLY_GATHER
+#define DLBC_WAVE_EARLY_GATHER 0
+#endif
 constexpr int WAVE_SEG = 128;  // sites per item == threads per block of the register-path kernel
 
 // Persistent 128-thread blocks (4 per SM): each block loops over tickets; an item is a 128-site row
@@ -154,7 +157,7 @@ constexpr int WAVE_SEG = 128;  // sites per item == threads per block of the reg
 // prefetched ticket of a block that is itself working on a still smaller one: the chain ends at
 // a running item, so there is no deadlock.
 template <int C, int EQ, int PSI, bool MASK, bool EXACT>
-__global__ void __launch_bounds__(WAVE_SEG, (MASK ? DLBC_MASK_BLOCKS : 4))
+__global__ void __launch_bounds__(WAVE_SEG, (MASK ? DLBC_MASK_BLOCKS_WAVE : 4))
 wave_kernel(Geom g, Fields fl, StepParams P, Wave w) {
   __shared__ int s_ticket[2];
   const bool lead = threadIdx.x == 0;
@@ -172,6 +175,15 @@ wave_kernel(Geom g, Fields fl, StepParams P, Wave w) {
       __syncthreads();  // all psi stores of the block precede (CTA scope) the lead thread's release below
       if (lead) red_release_add(w.sync + wi.cnt + wi.zg * (w.tyb + 2) + wi.row, 1);
     } else if (wi.kind == 2) {
+#if DLBC_WAVE_EARLY_GATHER
+      // the gather of the populations depends on nothing written in this launch: issue it BEFORE the wait for psi,
+      // so that the poll's round trips, the fence and the block barrier overlap the DRAM latency of the 19 C loads
+      Nbr n = {};
+      uint32_t bits = 0;
+      double f[C][Q];
+      bool go = false;
+      if (x < g.nx) go = fused_gather<C, MASK, POL_STREAM>(g, fl, x, wi.y, wi.zg, n, bits, f);
+#endif
       if (threadIdx.x < 32) {
         if (threadIdx.x < 9) {
           const int *c = wave_wait_counter(g, w, wi, threadIdx.x);
@@ -181,7 +193,11 @@ wave_kernel(Geom g, Fields fl, StepParams P, Wave w) {
         wave_acquire();  // of one per straggler (1.56 fences per item measured); the warp barrier orders every poll before it
       }
       __syncthreads();
+#if DLBC_WAVE_EARLY_GATHER
+      if (go) fused_finish<C, EQ, true, MASK, EXACT, true, POL_STREAM>(g, fl, P, wi.zg, n, bits, f);
+#else
       if (x < g.nx) fused_site<C, EQ, true, MASK, EXACT, true, POL_STREAM>(g, fl, P, x, wi.y, wi.zg);
+#endif
     }
     if (lead) s_ticket[it] = nxt;
     __syncthreads();
