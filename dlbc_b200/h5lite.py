@@ -375,8 +375,69 @@ def _string_attr(name, strings, gheap, gheap_addr_slot):
     return m
 
 
-def write_file(path, array, name="OutArray", input_lines=None, metadata=None, globals_=None):
-    """Write `array` (float64 or int32, C order) as the contiguous dataset /<name> of a new HDF5 file, with the
+_CHUNK_K = 32  # indexed-storage internal node K of a version-0 superblock (fixed: the field only exists from v1 on)
+
+
+def _chunk_index(a, chunks, o_tree):
+    """Chunked storage of `a` (io/hdf5.d:237-241: `writeChunked = true` makes every rank's block one chunk): returns
+    (tree bytes, [chunk bytes ...]) for a version-1 B-tree of node type 1 placed at file offset o_tree with the raw
+    chunks stored back to back right after it.  Chunks are whole (edge chunks are padded with zeros, as libhdf5 stores
+    them), unfiltered, keyed by their element offsets + a trailing 0 for the element-size dimension; the key after the
+    last one of a node is `last chunk offset + chunk dims` as in the files libhdf5 writes.  One leaf holds up to
+    2K = 64 chunks; more chunks get one internal node above up to 64 leaves."""
+    nd, es = a.ndim, a.dtype.itemsize
+    if len(chunks) != nd or any(int(c) < 1 for c in chunks):
+        raise H5Error(f"chunk dims {chunks} do not fit an array of rank {nd}")
+    chunks = tuple(int(c) for c in chunks)
+    grid = [(s + c - 1) // c for s, c in zip(a.shape, chunks)]
+    offs_list = [tuple(int(i) * c for i, c in zip(idx, chunks)) for idx in np.ndindex(*grid)]
+    cap = 2 * _CHUNK_K
+    if len(offs_list) > cap * cap:
+        raise H5Error(f"{len(offs_list)} chunks: more than a two-level index holds ({cap * cap})")
+    csize = int(np.prod(chunks)) * es
+    keysz = 8 + 8 * (nd + 1)
+    node_size = 24 + (cap + 1) * keysz + cap * 8
+    leaves = [offs_list[i:i + cap] for i in range(0, len(offs_list), cap)]
+    n_nodes = len(leaves) + (1 if len(leaves) > 1 else 0)
+    o_chunks = o_tree + n_nodes * node_size
+
+    def key(size, offs):
+        return struct.pack("<II", size, 0) + struct.pack(f"<{nd + 1}Q", *offs, 0)
+
+    def end_key(offs):
+        return struct.pack("<II", 0, 0) + struct.pack(f"<{nd + 1}Q", *[o + c for o, c in zip(offs, chunks)], es)
+
+    def node(level, entries, left, right):  # entries: [(offsets, child address)]
+        b = b"TREE" + struct.pack("<BBHQQ", 1, level, len(entries), left, right)
+        for offs, child in entries:
+            b += key(csize, offs) + struct.pack("<Q", child)
+        b += end_key(entries[-1][0])
+        return b + b"\0" * (node_size - len(b))
+
+    first_leaf = o_tree + (node_size if len(leaves) > 1 else 0)
+    tree, k = b"", 0
+    for i, lf in enumerate(leaves):
+        left = first_leaf + (i - 1) * node_size if i > 0 else _UNDEF
+        right = first_leaf + (i + 1) * node_size if i + 1 < len(leaves) else _UNDEF
+        tree += node(0, [(o, o_chunks + (k + j) * csize) for j, o in enumerate(lf)], left, right)
+        k += len(lf)
+    if len(leaves) > 1:
+        tree = node(1, [(lf[0], first_leaf + i * node_size) for i, lf in enumerate(leaves)], _UNDEF, _UNDEF) + tree
+    data = []
+    for offs in offs_list:
+        blk = a[tuple(slice(o, o + c) for o, c in zip(offs, chunks))]
+        if blk.shape != chunks:
+            full = np.zeros(chunks, a.dtype)
+            full[tuple(slice(0, n) for n in blk.shape)] = blk
+            blk = full
+        data.append(np.ascontiguousarray(blk).tobytes())
+    return tree, data
+
+
+def write_file(path, array, name="OutArray", input_lines=None, metadata=None, globals_=None, chunks=None):
+    """Write `array` (float64 or int32, C order) as the dataset /<name> of a new HDF5 file -- contiguous, or chunked
+    when `chunks` (chunk dims, one per array dimension) is given: the reference's `hdf5.writeChunked = true` form,
+    where the chunk is one rank's block (io/hdf5.d:237-241; replay.write_outputs passes the z-slab) --, with the
     attributes the reference adds to every field file (io/hdf5.d:264-285): `input` on the root group -- the lines of
     the parameter file, from which the reference can re-read its parameters (parameters.d:172-174,339-351) --, the
     group `metadata` with string / int attributes (revision info, hdf5.d:290-299) and, for checkpoint files, the
@@ -439,13 +500,25 @@ def write_file(path, array, name="OutArray", input_lines=None, metadata=None, gl
     rank = a.ndim
     dataspace = struct.pack("<BBBx4x", 1, rank, 0) + struct.pack(f"<{rank}Q", *a.shape)
     fill = bytes([2, 2, 2, 1, 0, 0, 0, 0])                      # v2: late allocation, fill if set, default value
+    if chunks is None:
+        layout0 = struct.pack("<BBQQ", 3, 1, 0, 0)
+    else:
+        layout0 = struct.pack("<BBBQ", 3, 2, rank + 1, 0) + struct.pack(f"<{rank + 1}I", *([1] * rank), a.dtype.itemsize)
     dset_len = 16 + len(_msg(0x01, dataspace)) + len(_msg(0x03, _datatype(a.dtype))) + len(_msg(0x05, fill)) + \
-        len(_msg(0x08, struct.pack("<BBQQ", 3, 1, 0, 0)))
+        len(_msg(0x08, layout0))
     o += dset_len
     o_gheap = (o + 7) // 8 * 8
     o = o_gheap + (gheap.size() if gheap.objs else 0)
     o_data = (o + 7) // 8 * 8
-    eof = o_data + a.nbytes
+    if chunks is None:
+        payload = [a.tobytes()]
+        layout = struct.pack("<BBQQ", 3, 1, o_data, a.nbytes)
+    else:
+        tree, payload = _chunk_index(a, chunks, o_data)
+        payload = [tree] + payload
+        layout = struct.pack("<BBBQ", 3, 2, rank + 1, o_data) + struct.pack(f"<{rank + 1}I", *[int(c) for c in chunks],
+                                                                            a.dtype.itemsize)
+    eof = o_data + sum(len(b) for b in payload)
     for m, offs in patches:
         for k in offs:
             struct.pack_into("<Q", m, k, o_gheap)
@@ -476,8 +549,7 @@ def write_file(path, array, name="OutArray", input_lines=None, metadata=None, gl
         assert len(blob) == gp["ohdr"]
         blob += gh + gb + ghp
     assert len(blob) == o_dset
-    dset = _ohdr([_msg(0x01, dataspace), _msg(0x03, _datatype(a.dtype)), _msg(0x05, fill),
-                  _msg(0x08, struct.pack("<BBQQ", 3, 1, o_data, a.nbytes))])
+    dset = _ohdr([_msg(0x01, dataspace), _msg(0x03, _datatype(a.dtype)), _msg(0x05, fill), _msg(0x08, layout)])
     assert len(dset) == dset_len
     blob += dset
     blob += b"\0" * (o_gheap - len(blob))
@@ -486,13 +558,14 @@ def write_file(path, array, name="OutArray", input_lines=None, metadata=None, gl
     blob += b"\0" * (o_data - len(blob))
     with open(path, "wb") as fh:
         fh.write(blob)
-        fh.write(a.tobytes())
+        for b in payload:
+            fh.write(b)
     return path
 
 
-def write_dataset(path, array, name="OutArray"):
-    """A bare contiguous dataset /<name> (no attributes)."""
-    return write_file(path, array, name)
+def write_dataset(path, array, name="OutArray", chunks=None):
+    """A bare dataset /<name> (no attributes), contiguous or chunked."""
+    return write_file(path, array, name, chunks=chunks)
 
 
 def field_file_name(field, simulation_name, timestep, time_id="00000000T000000"):

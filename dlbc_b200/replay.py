@@ -255,10 +255,12 @@ def write_checkpoint(L, p, t, directory, input_lines=None, run_id="00000000T0000
     meta = metadata()
     paths = []
     for i in range(int(p["lb.components"])):
-        paths.append(h5lite.write_file(os.path.join(d, f"cp-fluids{i}-{sim}-{run_id}-t{t:08d}.h5"), L.get_populations(i),
-                                       input_lines=input_lines, metadata=meta, globals_={"dlbc.lb.lb.timestep": int(t)}))
-    paths.append(h5lite.write_file(os.path.join(d, f"cp-mask-{sim}-{run_id}-t{t:08d}.h5"), L.get_mask().astype(np.int32),
-                                   input_lines=input_lines, metadata=meta, globals_={"dlbc.lb.lb.timestep": int(t)}))
+        f = L.get_populations(i)
+        paths.append(h5lite.write_file(os.path.join(d, f"cp-fluids{i}-{sim}-{run_id}-t{t:08d}.h5"), f, input_lines=input_lines,
+                                       metadata=meta, globals_={"dlbc.lb.lb.timestep": int(t)}, chunks=chunk_block(p, f.shape)))
+    m = L.get_mask().astype(np.int32)
+    paths.append(h5lite.write_file(os.path.join(d, f"cp-mask-{sim}-{run_id}-t{t:08d}.h5"), m, input_lines=input_lines,
+                                   metadata=meta, globals_={"dlbc.lb.lb.timestep": int(t)}, chunks=chunk_block(p, m.shape)))
     return paths
 
 
@@ -321,17 +323,31 @@ def replay(p, make_lattice=None, device_init=False, restore=None, base_dir=".", 
     return out
 
 
-def write_outputs(out, directory, run_id="00000000T000000", input_lines=None):
+def chunk_block(p, shape):
+    """The chunk of a `hdf5.writeChunked = true` file (io/hdf5.d:150-200,237-241): one rank's block -- the global
+    extent divided by the process grid `parallel.nc` (a 0 or missing entry counts as 1 here: this library's ranks are
+    z-slabs and the replay driver is one process) -- times the whole vector length of a vector field.  None when
+    the parameter set asks for contiguous files."""
+    if p is None or not p.get("io.hdf5.writeChunked", False):
+        return None
+    nc = [int(v) if int(v) > 0 else 1 for v in p.get("parallel.nc", [])]
+    nc += [1] * (3 - len(nc))
+    return tuple(-(-int(n) // nc[d]) if d < 3 else int(n) for d, n in enumerate(shape))
+
+
+def write_outputs(out, directory, run_id="00000000T000000", input_lines=None, params=None):
     """Write every collected field as the reference would name and furnish it (io/io.d:157-172, io/hdf5.d:264-299):
-    <field>-<sim>-<run id>-t%08d.h5 with one contiguous /OutArray dataset, the `input` attribute (the parameter
-    file, so that any output file can serve as input file again) and the `metadata` group."""
+    <field>-<sim>-<run id>-t%08d.h5 with one /OutArray dataset (contiguous, or chunked by rank block when `params`
+    has hdf5.writeChunked = true), the `input` attribute (the parameter file, so that any output file can serve as
+    input file again) and the `metadata` group."""
     from . import h5lite
     os.makedirs(directory, exist_ok=True)
     paths = []
     for k, v in out.items():
         stem, t = k.rsplit("-t", 1)
         paths.append(h5lite.write_file(os.path.join(directory, f"{stem}-{run_id}-t{t}.h5"), v, input_lines=input_lines,
-                                       metadata=metadata() if input_lines is not None else None))
+                                       metadata=metadata() if input_lines is not None else None,
+                                       chunks=chunk_block(params, np.shape(v))))
     return paths
 
 
@@ -357,7 +373,7 @@ def main(argv=None):
     for k, v in out.items():
         print(f"{k}: shape {v.shape}, sum {float(np.sum(v)):.15g}")
     if a.out:
-        write_outputs(out, a.out, a.run_id, input_lines=lines)
+        write_outputs(out, a.out, a.run_id, input_lines=lines, params=p)
 
 
 if __name__ == "__main__":

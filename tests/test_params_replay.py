@@ -331,6 +331,66 @@ def test_replay_outputs_as_reference_named_hdf5(tmp_path, golden):
     assert_bitexact(H.read_dataset(str(f)), golden("bdist2-3d")["population-red-t10"], "population-red t10 from the HDF5 file")
 
 
+def test_chunked_writer_round_trip_and_structure(tmp_path):
+    """hdf5.writeChunked = true (io/hdf5.d:237-241): layout class 2 + a version-1 chunk B-tree with the conventions of
+    the libhdf5-written files under the reference's reference-data (key after the last = last offset + chunk dims,
+    element size as trailing dimension), one leaf up to 64 chunks, an internal node above that; edge chunks padded."""
+    import struct
+    from dlbc_b200 import h5lite as H
+
+    rng = np.random.default_rng(4)
+    f = str(tmp_path / "c.h5")
+    for shape, chunks, levels in [((16, 12, 10, 19), (16, 12, 5, 19), 1), ((8, 8, 8), (8, 4, 4), 1), ((9, 9, 9), (2, 2, 2), 2),
+                                  ((20, 6, 70), (20, 6, 1), 2), ((6, 5), (6, 5), 1)]:
+        for dt in (np.float64, np.int32):
+            a = (rng.random(shape) * 1000).astype(dt)
+            H.write_file(f, a, input_lines=["x = 1"], metadata={"revisionHash": "h"}, globals_={"dlbc.lb.lb.timestep": 3},
+                         chunks=chunks)
+            assert_bitexact(H.read_dataset(f), a, f"chunked {shape} by {chunks}")
+            assert H.read_attributes(f)["input"] == ["x = 1"]
+            assert H.read_attributes(f, "globals") == {"dlbc.lb.lb.timestep": 3}
+            hf = H._File(f)
+            lay = [b for t, b in hf.messages(hf.links()["OutArray"]["ohdr"]) if t == 0x08][0]
+            nd = len(shape)
+            assert lay[0] == 3 and lay[1] == 2 and lay[2] == nd + 1
+            bt = struct.unpack_from("<Q", lay, 3)[0]
+            assert struct.unpack_from(f"<{nd + 1}I", lay, 11) == tuple(chunks) + (a.dtype.itemsize,)
+            raw = hf.b
+            assert raw[bt:bt + 4] == b"TREE" and raw[bt + 4] == 1 and raw[bt + 5] == levels - 1
+            used = hf.u16(bt + 6)
+            keysz = 8 + 8 * (nd + 1)
+            first = struct.unpack_from(f"<II{nd + 1}Q", raw, bt + 24)
+            assert first[0] == int(np.prod(chunks)) * a.dtype.itemsize and first[2:] == (0,) * (nd + 1)
+            if levels == 1:
+                grid = [-(-s // c) for s, c in zip(shape, chunks)]
+                assert used == int(np.prod(grid))
+                last = struct.unpack_from(f"<II{nd + 1}Q", raw, bt + 24 + used * (keysz + 8))
+                want = tuple((g - 1) * c + c for g, c in zip(grid, chunks)) + (a.dtype.itemsize,)
+                assert last[0] == 0 and last[2:] == want
+    with pytest.raises(H.H5Error):
+        H.write_file(f, np.zeros((4, 4)), chunks=(4,))
+    with pytest.raises(H.H5Error):
+        H.write_file(f, np.zeros((130, 130)), chunks=(1, 1))  # 16900 chunks > 64 * 64
+
+
+def test_replay_writes_chunked_files_when_asked(tmp_path, golden):
+    """writeChunked = true + parallel.nc: the chunk is one rank's block (the whole vector for populations)."""
+    import struct
+    from dlbc_b200 import h5lite as H
+
+    p = P.parse_file(os.path.join(IN, "bdist2-3d.in"), ["io.hdf5.writeChunked=true", "parallel.nc=[1,2,4]"])
+    assert R.chunk_block(p, (16, 16, 16, 19)) == (16, 8, 4, 19) and R.chunk_block(p, (16, 16, 16)) == (16, 8, 4)
+    assert R.chunk_block(P.parse_file(os.path.join(IN, "bdist2-3d.in")), (16, 16, 16)) is None
+    R.write_outputs(R.replay(p, make_lattice=_oracle_lattice), str(tmp_path), "20260101T000000", params=p)
+    f = str(tmp_path / "population-red-bdist2-3d-20260101T000000-t00000010.h5")
+    want = golden("bdist2-3d")["population-red-t10"]
+    assert_bitexact(H.read_dataset(f), want, "population-red t10 from the chunked file")
+    hf = H._File(f)
+    lay = [b for t, b in hf.messages(hf.links()["OutArray"]["ohdr"]) if t == 0x08][0]
+    gn = want.shape[:3]
+    assert lay[1] == 2 and struct.unpack_from("<5I", lay, 11) == (gn[0], gn[1] // 2, gn[2] // 4, 19, 8)
+
+
 @pytest.mark.gpu
 def test_replay_cli_on_the_gpu(tmp_path, golden):
     from dlbc_b200 import h5lite as H
