@@ -25,7 +25,8 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-O2,-Wall", "-I
 
 
 def units():
-    u = [("dlbc_cuda.cu", []), ("field_io.cu", ["-fmad=false"]), ("no_alloc.cu", ["-fmad=false"])]
+    u = [("dlbc_cuda.cu", []), ("field_io.cu", ["-fmad=false"]), ("no_alloc.cu", ["-fmad=false"]),
+         ("d2q9.cu", ["-fmad=false"])]
     for n in (1, 2, 3, 4):
         u.append((f"step_c{n}_exact.cu", ["-fmad=false"]))
         u.append((f"step_c{n}_fast.cu", ["-fmad=true"]))

@@ -9,9 +9,11 @@
 #include "kernels.h"
 
 struct ncclComm;
+namespace dlbc { namespace d2 { struct Lattice2; } }
 
 struct dlbc_cuda_ctx {
   dlbc_cuda_config cfg{};
+  dlbc::d2::Lattice2 *d2 = nullptr;   // a 2-D (D2Q9) context: everything else below is unused, see d2q9.cu
   dlbc::Geom g{};
   dlbc::StepParams p{};
   int device = 0;

@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "context.h"
+#include "d2q9.h"
 #include "field_io.h"
 #include "nccl_dyn.h"
 
@@ -68,6 +69,16 @@ int nccl_fail(dlbc_cuda_ctx *ctx, const char *what, ncclResult_t r) {
 #define ARG(cond, msg)                                                 \
   do {                                                                 \
     if (!(cond)) return set_error(ctx, std::string("dlbc_cuda: ") + msg, 1); \
+  } while (0)
+
+// entry points that serve 2-D (D2Q9) contexts hand over to d2q9.cu before anything else
+#define D2(call)                                                             \
+  do {                                                                       \
+    if (ctx && ctx->d2) {                                                    \
+      cudaError_t e2_ = cudaSetDevice(ctx->device);                          \
+      if (e2_ != cudaSuccess) return cuda_fail(ctx, "cudaSetDevice", e2_);   \
+      return d2::call;                                                       \
+    }                                                                        \
   } while (0)
 
 bool is_pow2(double x) {
@@ -395,6 +406,7 @@ int join_comm(dlbc_cuda_ctx *ctx) {
 
 int check_ctx(dlbc_cuda_ctx *ctx) {
   if (!ctx) return set_error(nullptr, "dlbc_cuda: null context", 1);
+  if (ctx->d2) return set_error(ctx, "dlbc_cuda: this entry point is not available on a 2-D (D2Q9) context", 1);
   cudaError_t e = cudaSetDevice(ctx->device);
   if (e != cudaSuccess) return cuda_fail(ctx, "cudaSetDevice", e);
   return 0;
@@ -571,6 +583,7 @@ int dlbc_cuda_destroy(dlbc_cuda_ctx *ctx) {
   if (!ctx) return 0;
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
+  if (ctx->d2) d2::destroy(ctx->d2);
   if (ctx->nccl) nccl_api().CommDestroy(ctx->nccl);
   for (double *p : {ctx->f[0], ctx->f[1], ctx->psi, ctx->rho_wall, ctx->partial}) if (p) cudaFree(p);
   if (ctx->mask) cudaFree(ctx->mask);
@@ -592,8 +605,30 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
   ARG(cfg && out, "create: null pointer");
   *out = nullptr;
   ARG(cfg->abi_version == DLBC_CUDA_ABI_VERSION, "create: abi_version mismatch");
-  ARG(cfg->d == 3 && cfg->q == 19, "create: only the D3Q19 lattice is built (connectivity.d:21-32)");
+  ARG((cfg->d == 3 && cfg->q == 19) || (cfg->d == 2 && cfg->q == 9),
+      "create: the lattices built are D3Q19 and D2Q9 (connectivity.d:21-32)");
   ARG(cfg->ncomp >= 1 && cfg->ncomp <= DLBC_CUDA_MAX_COMPONENTS, "create: ncomp out of range");
+  if (cfg->d == 2) {
+    // Lattice!(d2q9): its own small set of kernels and arrays (d2q9.cu), one rank; gn[2] is ignored (0 or 1)
+    ARG(cfg->psi_form == DLBC_PSI_LINEAR || cfg->psi_form == DLBC_PSI_EXPONENTIAL, "create: bad psi_form");
+    ARG(cfg->eqdist_form >= 0 && cfg->eqdist_form <= 2, "create: bad eqdist_form");
+    for (int c = 0; c < cfg->ncomp; c++) ARG(cfg->tau[c] > 0.0 && std::isfinite(cfg->tau[c]), "create: tau must be positive");
+    int ndev2 = 0;
+    cudaError_t e2 = cudaGetDeviceCount(&ndev2);
+    if (e2 != cudaSuccess || ndev2 == 0)
+      return set_error(nullptr, std::string("dlbc_cuda_create: no CUDA device (") + cudaGetErrorString(e2) +
+                                    "); this library has no CPU fallback", 1000 + (int)e2);
+    ARG(cfg->device >= 0 && cfg->device < ndev2, "create: device ordinal out of range");
+    d2::Lattice2 *l2 = nullptr;
+    const int rc = d2::create(*cfg, &l2, g_create_error);
+    if (rc) return rc;
+    ctx = new dlbc_cuda_ctx();
+    ctx->cfg = *cfg;
+    ctx->device = cfg->device;
+    ctx->d2 = l2;
+    *out = ctx;
+    return 0;
+  }
   ARG(cfg->nranks >= 1 && cfg->rank >= 0 && cfg->rank < cfg->nranks, "create: bad rank/nranks");
   for (int d = 0; d < 3; d++) ARG(cfg->gn[d] >= 1 && cfg->gn[d] <= 65535, "create: gn out of range (1..65535)");
   // lattice.d:178,233-241: the global size must be divisible by the process grid
@@ -771,6 +806,7 @@ int dlbc_cuda_upload_populations_xrange(dlbc_cuda_ctx *ctx, int comp, const doub
 }
 
 int dlbc_cuda_upload_populations(dlbc_cuda_ctx *ctx, int comp, const double *aos, int halo) {
+  D2(upload_populations(ctx->d2, comp, aos, halo, ctx->err));
   TRY(check_ctx(ctx));
   ARG(aos, "upload_populations: null pointer");
   ARG(halo >= 0, "upload_populations: negative halo");
@@ -802,6 +838,7 @@ int dlbc_cuda_download_populations_xrange(dlbc_cuda_ctx *ctx, int comp, double *
 }
 
 int dlbc_cuda_download_populations(dlbc_cuda_ctx *ctx, int comp, double *aos, int halo) {
+  D2(download_populations(ctx->d2, comp, aos, halo, ctx->err));
   TRY(check_ctx(ctx));
   ARG(aos, "download_populations: null pointer");
   ARG(halo >= 0, "download_populations: negative halo");
@@ -810,6 +847,7 @@ int dlbc_cuda_download_populations(dlbc_cuda_ctx *ctx, int comp, double *aos, in
 }
 
 int dlbc_cuda_upload_mask(dlbc_cuda_ctx *ctx, const int32_t *mask, int halo) {
+  D2(upload_mask(ctx->d2, mask, halo, ctx->err));
   TRY(check_ctx(ctx));
   ARG(mask, "upload_mask: null pointer");
   ARG(halo >= 0, "upload_mask: negative halo");
@@ -830,6 +868,7 @@ int dlbc_cuda_upload_mask(dlbc_cuda_ctx *ctx, const int32_t *mask, int halo) {
 }
 
 int dlbc_cuda_download_mask(dlbc_cuda_ctx *ctx, int32_t *mask, int halo) {
+  D2(download_mask(ctx->d2, mask, halo, ctx->err));
   TRY(check_ctx(ctx));
   ARG(mask, "download_mask: null pointer");
   ARG(halo >= 0, "download_mask: negative halo");
@@ -845,6 +884,13 @@ int dlbc_cuda_download_mask(dlbc_cuda_ctx *ctx, int32_t *mask, int halo) {
 
 // ---- the hot path ---------------------------------------------------------------------------
 int dlbc_cuda_step(dlbc_cuda_ctx *ctx, int nsteps) {
+  if (ctx && ctx->d2) {
+    cudaError_t e2 = cudaSetDevice(ctx->device);
+    if (e2 != cudaSuccess) return cuda_fail(ctx, "cudaSetDevice", e2);
+    const int rc = d2::step(ctx->d2, nsteps, ctx->err);
+    if (rc == 0) ctx->timestep += nsteps;
+    return rc;
+  }
   TRY(check_ctx(ctx));
   ARG(nsteps >= 0, "step: negative step count");
   if (nsteps == 0) return 0;
@@ -857,6 +903,7 @@ int dlbc_cuda_step(dlbc_cuda_ctx *ctx, int nsteps) {
 }
 
 int dlbc_cuda_sync(dlbc_cuda_ctx *ctx) {
+  D2(sync(ctx->d2, ctx->err));
   TRY(check_ctx(ctx));
   CK(cudaStreamSynchronize(ctx->compute));
   CK(cudaStreamSynchronize(ctx->comm));
@@ -868,6 +915,7 @@ int64_t dlbc_cuda_timestep(const dlbc_cuda_ctx *ctx) { return ctx ? ctx->timeste
 
 // ---- outputs --------------------------------------------------------------------------------
 int dlbc_cuda_download_density(dlbc_cuda_ctx *ctx, int comp, double *out, int halo) {
+  D2(download_field(ctx->d2, d2::F2_DENSITY, comp, comp, out, halo, ctx->err));
   TRY(check_ctx(ctx));
   ARG(out && halo >= 0, "download_density: bad argument");
   ARG(comp >= 0 && comp < ctx->cfg.ncomp, "download_density: component out of range");
@@ -875,6 +923,7 @@ int dlbc_cuda_download_density(dlbc_cuda_ctx *ctx, int comp, double *out, int ha
   return download_field(ctx, 0, comp, comp, nullptr, out, halo);
 }
 int dlbc_cuda_download_colour(dlbc_cuda_ctx *ctx, int comp1, int comp2, double *out, int halo) {
+  D2(download_field(ctx->d2, d2::F2_COLOUR, comp1, comp2, out, halo, ctx->err));
   TRY(check_ctx(ctx));
   ARG(out && halo >= 0, "download_colour: bad argument");
   ARG(comp1 >= 0 && comp1 < ctx->cfg.ncomp && comp2 >= 0 && comp2 < ctx->cfg.ncomp, "download_colour: component out of range");
@@ -882,6 +931,7 @@ int dlbc_cuda_download_colour(dlbc_cuda_ctx *ctx, int comp1, int comp2, double *
   return download_field(ctx, 1, comp1, comp2, nullptr, out, halo);
 }
 int dlbc_cuda_download_velocity(dlbc_cuda_ctx *ctx, int comp, double *out, int halo) {
+  D2(download_field(ctx->d2, d2::F2_VELOCITY, comp, comp, out, halo, ctx->err));
   TRY(check_ctx(ctx));
   ARG(out && halo >= 0, "download_velocity: bad argument");
   ARG(comp >= 0 && comp < ctx->cfg.ncomp, "download_velocity: component out of range");
@@ -890,6 +940,7 @@ int dlbc_cuda_download_velocity(dlbc_cuda_ctx *ctx, int comp, double *out, int h
 }
 
 int dlbc_cuda_download_force(dlbc_cuda_ctx *ctx, int comp, double *out, int halo) {
+  D2(download_field(ctx->d2, d2::F2_FORCE, comp, comp, out, halo, ctx->err));
   TRY(check_ctx(ctx));
   ARG(out && halo >= 0, "download_force: bad argument");
   ARG(comp >= 0 && comp < ctx->cfg.ncomp, "download_force: component out of range");
@@ -1086,6 +1137,14 @@ static int reduce_component(dlbc_cuda_ctx *ctx, int comp, double out4[4]) {
 }
 
 int dlbc_cuda_total_mass(dlbc_cuda_ctx *ctx, int comp, double *out) {
+  if (ctx && ctx->d2) {
+    double r2[4];
+    if (!out) return set_error(ctx, "dlbc_cuda: total_mass: null pointer", 1);
+    cudaSetDevice(ctx->device);
+    const int rc = d2::reduce(ctx->d2, comp, r2, ctx->err);
+    if (rc == 0) *out = r2[0];
+    return rc;
+  }
   TRY(check_ctx(ctx));
   ARG(out, "total_mass: null pointer");
   ARG(comp >= 0 && comp < ctx->cfg.ncomp, "total_mass: component out of range");
@@ -1095,6 +1154,14 @@ int dlbc_cuda_total_mass(dlbc_cuda_ctx *ctx, int comp, double *out) {
   return 0;
 }
 int dlbc_cuda_total_momentum(dlbc_cuda_ctx *ctx, int comp, double out[3]) {
+  if (ctx && ctx->d2) {
+    double r2[4];
+    if (!out) return set_error(ctx, "dlbc_cuda: total_momentum: null pointer", 1);
+    cudaSetDevice(ctx->device);
+    const int rc = d2::reduce(ctx->d2, comp, r2, ctx->err);
+    if (rc == 0) { out[0] = r2[1]; out[1] = r2[2]; out[2] = 0.0; }
+    return rc;
+  }
   TRY(check_ctx(ctx));
   ARG(out, "total_momentum: null pointer");
   ARG(comp >= 0 && comp < ctx->cfg.ncomp, "total_momentum: component out of range");
@@ -1141,19 +1208,19 @@ int dlbc_cuda_site_function(int device, int fn, int form, int n, const double *i
 
 int dlbc_cuda_launch_count(const dlbc_cuda_ctx *ctx, int64_t *count) {
   if (!ctx || !count) return 1;
-  *count = ctx->launches;
+  *count = ctx->d2 ? d2::launches(ctx->d2) : ctx->launches;
   return 0;
 }
 
 int dlbc_cuda_device_bytes(const dlbc_cuda_ctx *ctx, int64_t *bytes) {
   if (!ctx || !bytes) return 1;
-  *bytes = ctx->device_bytes;
+  *bytes = ctx->d2 ? d2::device_bytes(ctx->d2) : ctx->device_bytes;
   return 0;
 }
 
 int dlbc_cuda_kernel_variant(const dlbc_cuda_ctx *ctx, int *variant) {
   if (!ctx || !variant) return 1;
-  *variant = effective_variant(ctx);
+  *variant = ctx->d2 ? DLBC_KERNEL_TWO_PASS : effective_variant(ctx);
   return 0;
 }
 

@@ -38,18 +38,26 @@ class Lattice:
         self._l = _lib.load()
         self._h = None
         gn = tuple(int(x) for x in gn)
-        if len(gn) != 3:
-            raise ValueError("the CUDA path is built for the D3Q19 lattice: gn must have 3 entries")
+        if len(gn) not in (2, 3):
+            raise ValueError("the CUDA path is built for D3Q19 (gn with 3 entries) and D2Q9 (2 entries)")
         self.gn = gn
+        self.d = len(gn)
+        self.q = Q if self.d == 3 else 9  # Lattice!(d3q19) / Lattice!(d2q9), connectivity.d:21-32
         self.ncomp = int(components)
         self.rank, self.nranks = int(rank), int(nranks)
-        z0, z1 = slab_range(gn[2], self.rank, self.nranks)
-        self.z_range = (z0, z1)
-        self.n = (gn[0], gn[1], z1 - z0)  # local physical extents
+        if self.d == 3:
+            z0, z1 = slab_range(gn[2], self.rank, self.nranks)
+            self.z_range = (z0, z1)
+            self.n = (gn[0], gn[1], z1 - z0)  # local physical extents
+        else:
+            if self.nranks != 1:
+                raise ValueError("a 2-D lattice runs on one rank")
+            self.z_range = (0, 1)
+            self.n = gn
         cfg = _lib.Config()
         cfg.abi_version = _lib.ABI_VERSION
-        cfg.d, cfg.q = 3, Q
-        for i in range(3):
+        cfg.d, cfg.q = self.d, self.q
+        for i in range(self.d):
             cfg.gn[i] = gn[i]
         cfg.ncomp = self.ncomp
         if self.ncomp < 1 or self.ncomp > _lib.MAXC:
@@ -120,12 +128,12 @@ class Lattice:
     def set_populations(self, comp, aos, halo=0):
         """L.fluids[comp] <- aos ([x][y][z][19] incl. `halo` layers: Field.arr when halo = 2)."""
         a = np.ascontiguousarray(aos, dtype=np.float64)
-        if a.shape != self._shape(halo, (Q,)):
-            raise ValueError(f"populations shape {a.shape} != {self._shape(halo, (Q,))}")
+        if a.shape != self._shape(halo, (self.q,)):
+            raise ValueError(f"populations shape {a.shape} != {self._shape(halo, (self.q,))}")
         self._ck(self._l.dlbc_cuda_upload_populations(self._h, comp, _dp(a), halo))
 
     def get_populations(self, comp, halo=0):
-        out = np.zeros(self._shape(halo, (Q,)))
+        out = np.zeros(self._shape(halo, (self.q,)))
         self._ck(self._l.dlbc_cuda_download_populations(self._h, comp, _dp(out), halo))
         return out
 
@@ -177,12 +185,12 @@ class Lattice:
         return out
 
     def velocity(self, comp):
-        out = np.empty(self.n + (3,))
+        out = np.empty(self.n + (self.d,))
         self._ck(self._l.dlbc_cuda_download_velocity(self._h, comp, _dp(out), 0))
         return out
 
     def force(self, comp):
-        out = np.empty(self.n + (3,))
+        out = np.empty(self.n + (self.d,))
         self._ck(self._l.dlbc_cuda_download_force(self._h, comp, _dp(out), 0))
         return out
 

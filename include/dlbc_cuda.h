@@ -70,8 +70,14 @@ enum {
  * (lb/force.d:26-43), lb.eqdist.eqDistForm (lb/eqdist.d:18), parallel.nc (parallel.d:34). */
 typedef struct dlbc_cuda_config {
   int32_t abi_version;            /* DLBC_CUDA_ABI_VERSION */
-  int32_t d, q;                   /* must be 3, 19 (connectivity.d:21-32 default gconn) */
-  int64_t gn[3];                  /* global physical lattice size */
+  int32_t d, q;                   /* 3, 19 (connectivity.d:21-32 default gconn) or 2, 9 (version(D2Q9), :27-29): a
+                                     2-D context (csrc/d2q9.cu) runs on one rank and serves create / destroy,
+                                     upload / download of populations and mask ([x][y][9], [x][y]), step, sync,
+                                     timestep, download_density / colour / velocity / force ([x][y] and
+                                     [x][y][2]), total_mass, total_momentum (z = 0), launch_count, device_bytes,
+                                     kernel_variant; every other entry point fails on it with a message.
+                                     Arithmetic there is always the reference's operation order */
+  int64_t gn[3];                  /* global physical lattice size (gn[2]: 0 or 1 when d = 2) */
   int32_t ncomp;                  /* 1..DLBC_CUDA_MAX_COMPONENTS */
   double tau[DLBC_CUDA_MAX_COMPONENTS];
   double gcc[DLBC_CUDA_MAX_COMPONENTS * DLBC_CUDA_MAX_COMPONENTS]; /* row-major [f1][f2] */
