@@ -23,10 +23,11 @@ import numpy as np
 
 from . import init as I
 from . import params as P
-from .connectivity import d3q19
+from .connectivity import d2q9, d3q19
 from .rng import Mt19937
 
 AXIS = {"X": 0, "Y": 1, "Z": 2}
+CONN = {2: d2q9, 3: d3q19}
 
 
 class ReplayError(ValueError):
@@ -48,14 +49,14 @@ def _fit(v, n, name, strict=False, fill=0):
 def lattice_kwargs(p):
     """Parameter dict -> (gn, components, kwargs of Lattice / OracleLattice)."""
     gn = tuple(int(x) for x in p["lattice.gn"])
-    if len(gn) != 3:
-        raise ReplayError(f"lattice.gn = {list(gn)}: libdlbc_cuda implements D3Q19 only")
+    if len(gn) not in (2, 3):
+        raise ReplayError(f"lattice.gn = {list(gn)}: libdlbc_cuda implements D3Q19 (3-D) and D2Q9 (2-D)")
     if p["elec.enableElec"]:
         raise ReplayError("elec.enableElec = true: electrokinetics is outside the GPU path")
     C = int(p["lb.components"])
     sc = bool(p["lb.force.enableShanChen"])
     kw = dict(tau=_fit(p["lb.tau"], C, "lb.lb.tau", strict=p["lb.timesteps"] > 0),
-              global_acc=_fit(p["lb.force.globalAcc"], 3, "lb.force.globalAcc", fill=0.0),
+              global_acc=_fit(p["lb.force.globalAcc"], len(gn), "lb.force.globalAcc", fill=0.0),
               psi_form=p["lb.force.psiForm"], eqdist_form=p["lb.eqdist.eqDistForm"], enable_shan_chen=sc)
     if sc:
         gcc = _fit(p["lb.force.gcc"], C, "lb.force.gcc", strict=True)
@@ -77,7 +78,7 @@ def initial_mask(p, blk):
     if kind == "Plates":
         return I.mask_plates(blk, axis, p["lb.mask.wallOffset"])
     if kind == "Walls":
-        dhw = _fit(p["lb.mask.dimensionHasWall"], 3, "lb.mask.dimensionHasWall", fill=[False, False])
+        dhw = _fit(p["lb.mask.dimensionHasWall"], len(p["lattice.gn"]), "lb.mask.dimensionHasWall", fill=[False, False])
         return I.mask_walls(blk, [_fit(x, 2, "lb.mask.dimensionHasWall[i]", fill=False) for x in dhw],
                             p["lb.mask.wallThickness"])
     raise ReplayError(f"lb.mask.maskInit = {kind} is not supported by the replay driver")
@@ -92,8 +93,10 @@ def initial_populations(p, blk, mask):
     perturb = _fit(p["lb.init.fluidPerturb"], C, "lb.init.fluidPerturb", fill=0.0)
     reseed = _fit(p["lb.init.randomReseed"], C, "lb.init.randomReseed", fill=False)
     seeds = _fit(p["lb.init.randomSeed"], C, "lb.init.randomSeed", fill=0)
-    off = _fit(p["lb.init.initOffset"], 3, "lb.init.initOffset", fill=0.0)
-    sep = _fit(p["lb.init.initSeparation"], 3, "lb.init.initSeparation", fill=0.0)
+    nd = len(p["lattice.gn"])
+    conn = CONN[nd]  # the connectivity of this lattice (gconn, connectivity.d:21-32): conn, or d2q9 on a 2-D lattice
+    off = _fit(p["lb.init.initOffset"], nd, "lb.init.initOffset", fill=0.0)
+    sep = _fit(p["lb.init.initSeparation"], nd, "lb.init.initSeparation", fill=0.0)
     axis = AXIS[p["lb.init.initAxis"]]
     radius, thick = p["lb.init.initRadius"], p["lb.init.interfaceThickness"]
     widths = list(p["lb.init.lamellaeWidths"])
@@ -107,33 +110,33 @@ def initial_populations(p, blk, mask):
             if len(d) != n:
                 raise ReplayError(f"Array parameter lb.init.fluidDensities[{f}] must have length {n}.")
         if k == "Const":
-            need(1); a = I.init_const(blk, 19, d[0])
+            need(1); a = I.init_const(blk, conn.q, d[0])
         elif k == "ConstRandom":
-            need(1); a = I.init_const_random(blk, 19, d[0], lrng)
+            need(1); a = I.init_const_random(blk, conn.q, d[0], lrng)
         elif k == "EqDist":
-            need(1); a = I.init_eq_dist(blk, d3q19, form, d[0])
+            need(1); a = I.init_eq_dist(blk, conn, form, d[0])
         elif k == "EqDistRandom":
-            need(1); a = I.init_eq_dist_random(blk, d3q19, form, d[0], lrng)
+            need(1); a = I.init_eq_dist_random(blk, conn, form, d[0], lrng)
         elif k == "EqDistPerturb":
-            need(1); a = I.init_eq_dist_perturb(blk, d3q19, form, d[0], perturb[f], lrng)
+            need(1); a = I.init_eq_dist_perturb(blk, conn, form, d[0], perturb[f], lrng)
         elif k == "EqDistPerturbFrac":
-            need(1); a = I.init_eq_dist_perturb_frac(blk, d3q19, form, d[0], perturb[f], lrng)
+            need(1); a = I.init_eq_dist_perturb_frac(blk, conn, form, d[0], perturb[f], lrng)
         elif k == "EqDistSphere":
-            need(2); a = I.init_eq_dist_sphere(blk, d3q19, form, d[0], d[1], radius, off, thick)
+            need(2); a = I.init_eq_dist_sphere(blk, conn, form, d[0], d[1], radius, off, thick)
         elif k == "EqDistSphereFrac":
-            need(2); a = I.init_eq_dist_sphere_frac(blk, d3q19, form, d[0], d[1], radius, off, thick)
+            need(2); a = I.init_eq_dist_sphere_frac(blk, conn, form, d[0], d[1], radius, off, thick)
         elif k == "EqDistTwoSpheres":
-            need(2); a = I.init_eq_dist_two_spheres(blk, d3q19, form, d[0], d[1], radius, off, thick, sep)
+            need(2); a = I.init_eq_dist_two_spheres(blk, conn, form, d[0], d[1], radius, off, thick, sep)
         elif k == "EqDistTwoSpheresFrac":
-            need(2); a = I.init_eq_dist_two_spheres_frac(blk, d3q19, form, d[0], d[1], radius, off, thick, sep)
+            need(2); a = I.init_eq_dist_two_spheres_frac(blk, conn, form, d[0], d[1], radius, off, thick, sep)
         elif k == "EqDistCylinder":
-            need(2); a = I.init_eq_dist_cylinder(blk, d3q19, form, d[0], d[1], axis, radius, off, thick)
+            need(2); a = I.init_eq_dist_cylinder(blk, conn, form, d[0], d[1], axis, radius, off, thick)
         elif k == "EqDistCylinderFrac":
-            need(2); a = I.init_eq_dist_cylinder_frac(blk, d3q19, form, d[0], d[1], axis, radius, off, thick)
+            need(2); a = I.init_eq_dist_cylinder_frac(blk, conn, form, d[0], d[1], axis, radius, off, thick)
         elif k == "EqDistLamellae":
-            need(len(widths)); a = I.init_eq_dist_lamellae(blk, d3q19, form, d, widths, axis, thick)
+            need(len(widths)); a = I.init_eq_dist_lamellae(blk, conn, form, d, widths, axis, thick)
         elif k == "EqDistLamellaeFrac":
-            need(len(widths)); a = I.init_eq_dist_lamellae_frac(blk, d3q19, form, d, widths, axis, thick)
+            need(len(widths)); a = I.init_eq_dist_lamellae_frac(blk, conn, form, d, widths, axis, thick)
         else:
             raise ReplayError(f"lb.init.fluidInit[{f}] = {k} is not supported by the replay driver")
         pops.append(I.init_eq_dist_wall(np.ascontiguousarray(a), mask))  # lb/init.d:121

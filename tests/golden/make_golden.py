@@ -69,7 +69,7 @@ def main():
     # --- technical/checkpoint-3d: its parameter file exists only as the `input` attribute of the output files
     # (the test's input file IS reference-data/colour-red-blue-checkpoint-3d-t00000000.h5): extracted to in/
     from dlbc_b200 import h5lite as _h5
-    _lines = _h5.read_attributes(os.path.join(REF, "technical/checkpoint-3d/reference-data/colour-red-blue-checkpoint-3d-t00000000.h5"))["input"]
+    _lines = _h5.read_attributes(os.path.join(T, "technical/checkpoint-3d/reference-data/colour-red-blue-checkpoint-3d-t00000000.h5"))["input"]
     with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "in", "checkpoint-3d.in"), "w") as _f:
         _f.write("\n".join(_lines) + "\n")
     # --- technical/checkpoint-3d: restart KAT (checkpoint populations + mask -> 5 steps)
@@ -108,6 +108,22 @@ def main():
         for c in ("red", "blue"):
             out[f"{name}-{c}"] = g(f"lb/init-2d/reference-data/population-{c}-fluid-init-{name}-2d-t00000000.h5")
     codec.save(os.path.join(HERE, "init-2d-random.npz"), **out)
+
+    # --- the 2-D (D2Q9) spec cases: what their fast runs compare (t = 0 and the fast run's last dump), whole arrays;
+    # the parameter files and JSON specs are copied to in/ byte for byte
+    import shutil
+    for case, times, data in (("bdist2-2d", (0, 10), ("density-red", "density-blue", "population-red", "population-blue")),
+                              ("bdist2-sc-2d", (0, 10), ("colour-red-blue", "density-red", "density-blue", "population-red",
+                                                         "population-blue")),
+                              ("merging-droplets-2d", (0, 100), ("colour-red-blue", "density-red", "density-blue",
+                                                                 "population-red", "population-blue"))):
+        out = {}
+        for t in times:
+            for d in data:
+                out[f"{d}-t{t}"] = g(f"lb/{case}/reference-data/{d}-{case}-*t{t:08d}.h5")
+        codec.save(os.path.join(HERE, case + ".npz"), **out)
+        for ext in (".in", ".json"):
+            shutil.copy(T + f"lb/{case}/{case}{ext}", os.path.join(HERE, "in", case + ext))
 
     for f in sorted(glob.glob(os.path.join(HERE, "*.npz"))):
         print(f"{os.path.getsize(f):9d}  {os.path.basename(f)}")

@@ -65,7 +65,7 @@ def test_reader_overrides_apply_after_the_file():
 def test_reader_accepts_every_fixture(name):
     p = P.parse_file(os.path.join(IN, name))
     gn, C, kw = R.lattice_kwargs(p)
-    assert len(gn) == 3 and C == 2 and len(kw["tau"]) == 2
+    assert len(gn) == (2 if name.endswith("-2d.in") else 3) and C == 2 and len(kw["tau"]) == 2 and len(kw["global_acc"]) == len(gn)
 
 
 def test_fname_tokens():
@@ -79,7 +79,8 @@ def test_fname_tokens():
 def test_driver_rejects_what_the_gpu_path_does_not_cover():
     base = "[lattice]\ngn = [8, 8, 8]\n[lb]\ncomponents = 1\ntau = [1.0]\ntimesteps = 1\n"
     with pytest.raises(R.ReplayError, match="D3Q19"):
-        R.lattice_kwargs(P.parse_text(base.replace("[8, 8, 8]", "[8, 8]")))
+        R.lattice_kwargs(P.parse_text(base.replace("[8, 8, 8]", "[8]")))  # the 1-D lattices (D1Q3, D1Q5) are not built
+    assert R.lattice_kwargs(P.parse_text(base.replace("[8, 8, 8]", "[8, 6]")))[0] == (8, 6)  # D2Q9 is
     with pytest.raises(R.ReplayError, match="electrokinetics"):
         R.lattice_kwargs(P.parse_text(base + "[elec]\nenableElec = true\n"))
     with pytest.raises(R.ReplayError, match="lb.lb.tau"):
@@ -137,7 +138,8 @@ def test_replay_reference_case_on_the_oracle(golden, case, times, tol):
 
 
 # ---- the reference's JSON test specifications (dlbct/test.py, compare.py) ------------------------------------
-SPECS = ["merging-droplets-3d", "bdist2-3d", "bdist2-sc-3d", "laplace-droplet-3d"]
+SPECS = ["merging-droplets-3d", "bdist2-3d", "bdist2-sc-3d", "laplace-droplet-3d",
+         "bdist2-2d", "bdist2-sc-2d", "merging-droplets-2d"]  # the last three: configuration d2q9 (csrc/d2q9.cu)
 
 
 def test_spec_reader():
@@ -164,7 +166,7 @@ def test_spec_driven_replay_on_the_oracle(golden, case):
     # carries no accuracy for its fast run; the others grant exactly this 1e-15)
     rep = TestSpec(os.path.join(IN, case + ".json")).run(golden(case), "fast", subtest=extra, make_lattice=_oracle_lattice,
                                                          floor=1e-15)
-    assert any(t == 10 for _, t, _, _ in rep) and all(d == 0.0 for _, t, d, _ in rep if t == 0)
+    assert any(t >= 10 for _, t, _, _ in rep) and all(d == 0.0 for _, t, d, _ in rep if t == 0)
 
 
 @pytest.mark.gpu
@@ -175,8 +177,11 @@ def test_spec_driven_replay_on_the_gpu(golden, case):
     10 steps -- the bound the reference itself grants non-DMD builds)."""
     from dlbc_b200.testspec import TestSpec
     extra = ["lb.io.laplaceFreq=0"] if case == "laplace-droplet-3d" else []
-    rep = TestSpec(os.path.join(IN, case + ".json")).run(golden(case), "fast", subtest=extra, arithmetic="exact", floor=1e-15)
-    assert any(t == 10 for _, t, _, _ in rep) and all(d == 0.0 for _, t, d, _ in rep if t == 0)
+    # merging-droplets-2d: its fast run is 100 steps, not 10 -- measured 1.06e-15 on the colour field (values ~0.7, i.e. 5 ulp
+    # after 100 steps of exp() that differ from Phobos' in the last bit); the spec's full run grants 1e-14 at t = 1000
+    floor = 2e-15 if case == "merging-droplets-2d" else 1e-15
+    rep = TestSpec(os.path.join(IN, case + ".json")).run(golden(case), "fast", subtest=extra, arithmetic="exact", floor=floor)
+    assert any(t >= 10 for _, t, _, _ in rep) and all(d == 0.0 for _, t, d, _ in rep if t == 0)
 
 
 # ---- technical/checkpoint-3d: the input file is an .h5, the state comes from a checkpoint (-r) ----------------
