@@ -701,6 +701,17 @@ int dlbc_cuda_create(const dlbc_cuda_config *cfg, dlbc_cuda_ctx **out) {
                  : (cfg->nranks == 1 || ctx->g.nz >= 160 ? DLBC_KERNEL_WAVE : DLBC_KERNEL_TWO_PASS);
   if (!cfg->enable_shan_chen) ctx->variant = DLBC_KERNEL_TWO_PASS;  // nothing to order: one fused kernel per step
 
+  if (const char *e_l2 = std::getenv("DLBC_L2_PERSIST_MB")) {
+    // experiment switch: size of the L2 set-aside for persisting (evict_last) lines; unset = the driver's default
+    int max_persist = 0;
+    CKC(cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, ctx->device));
+    size_t want = (size_t)std::atol(e_l2) << 20;
+    if (want > (size_t)max_persist) want = (size_t)max_persist;
+    CKC(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want));
+    size_t got = 0;
+    cudaDeviceGetLimit(&got, cudaLimitPersistingL2CacheSize);
+    std::fprintf(stderr, "dlbc_cuda: persisting L2 set-aside %zu MB (max %d MB)\n", got >> 20, max_persist >> 20);
+  }
   CKC(cudaStreamCreateWithFlags(&ctx->compute, cudaStreamNonBlocking));
   {
     // the boundary chain of a multi-rank step must overtake the interior kernel's queued blocks
