@@ -116,11 +116,12 @@ def main():
                               ("bdist2-sc-2d", (0, 10), ("colour-red-blue", "density-red", "density-blue", "population-red",
                                                          "population-blue")),
                               ("merging-droplets-2d", (0, 100), ("colour-red-blue", "density-red", "density-blue",
-                                                                 "population-red", "population-blue"))):
+                                                                 "population-red", "population-blue")),
+                              ("laplace-droplet-2d", (0, 100), ("colour-red-blue", "density-red", "density-blue"))):
         out = {}
         for t in times:
             for d in data:
-                out[f"{d}-t{t}"] = g(f"lb/{case}/reference-data/{d}-{case}-*t{t:08d}.h5")
+                out[f"{d}-t{t}"] = g(f"lb/{case}/reference-data/{d}-{case}*-t{t:08d}.h5")  # (laplace: ...-gcc3.6-...)
         codec.save(os.path.join(HERE, case + ".npz"), **out)
         for ext in (".in", ".json"):
             shutil.copy(T + f"lb/{case}/{case}{ext}", os.path.join(HERE, "in", case + ext))

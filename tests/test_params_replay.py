@@ -139,7 +139,7 @@ def test_replay_reference_case_on_the_oracle(golden, case, times, tol):
 
 # ---- the reference's JSON test specifications (dlbct/test.py, compare.py) ------------------------------------
 SPECS = ["merging-droplets-3d", "bdist2-3d", "bdist2-sc-3d", "laplace-droplet-3d",
-         "bdist2-2d", "bdist2-sc-2d", "merging-droplets-2d"]  # the last three: configuration d2q9 (csrc/d2q9.cu)
+         "bdist2-2d", "bdist2-sc-2d", "merging-droplets-2d", "laplace-droplet-2d"]  # the last four: configuration d2q9 (csrc/d2q9.cu)
 
 
 def test_spec_reader():
@@ -161,7 +161,7 @@ def test_spec_reader():
 def test_spec_driven_replay_on_the_oracle(golden, case):
     """the fast run of each 3-D spec, its OWN overrides and compare rules (exact at t = 0, `accuracy` absolute later)."""
     from dlbc_b200.testspec import TestSpec
-    extra = ["lb.io.laplaceFreq=0"] if case == "laplace-droplet-3d" else []
+    extra = ["lb.io.laplaceFreq=0"] if case.startswith("laplace-droplet") else []
     # floor: the oracle is gcc's arithmetic, "another compiler" than the DMD that wrote the goldens (the laplace spec
     # carries no accuracy for its fast run; the others grant exactly this 1e-15)
     rep = TestSpec(os.path.join(IN, case + ".json")).run(golden(case), "fast", subtest=extra, make_lattice=_oracle_lattice,
@@ -176,10 +176,10 @@ def test_spec_driven_replay_on_the_gpu(golden, case):
     floor the GPU needs as "another compiler" (its exp() is not Phobos': <= 1 ulp per psi, 1e-15 absolute after
     10 steps -- the bound the reference itself grants non-DMD builds)."""
     from dlbc_b200.testspec import TestSpec
-    extra = ["lb.io.laplaceFreq=0"] if case == "laplace-droplet-3d" else []
+    extra = ["lb.io.laplaceFreq=0"] if case.startswith("laplace-droplet") else []
     # merging-droplets-2d: its fast run is 100 steps, not 10 -- measured 1.06e-15 on the colour field (values ~0.7, i.e. 5 ulp
     # after 100 steps of exp() that differ from Phobos' in the last bit); the spec's full run grants 1e-14 at t = 1000
-    floor = 2e-15 if case == "merging-droplets-2d" else 1e-15
+    floor = 2e-15 if case in ("merging-droplets-2d", "laplace-droplet-2d") else 1e-15  # (both: 100 steps)
     rep = TestSpec(os.path.join(IN, case + ".json")).run(golden(case), "fast", subtest=extra, arithmetic="exact", floor=floor)
     assert any(t >= 10 for _, t, _, _ in rep) and all(d == 0.0 for _, t, d, _ in rep if t == 0)
 
