@@ -55,7 +55,9 @@ def lattice_kwargs(p):
         raise ReplayError("elec.enableElec = true: electrokinetics is outside the GPU path")
     C = int(p["lb.components"])
     sc = bool(p["lb.force.enableShanChen"])
-    kw = dict(tau=_fit(p["lb.tau"], C, "lb.lb.tau", strict=p["lb.timesteps"] > 0),
+    # lb/init.d:99-105: a run that never collides does not need lb.tau (the reference zero-fills it; the lattice
+    # constructors want a positive value, which is then never used)
+    kw = dict(tau=_fit(p["lb.tau"], C, "lb.lb.tau", strict=p["lb.timesteps"] > 0, fill=1.0),
               global_acc=_fit(p["lb.force.globalAcc"], len(gn), "lb.force.globalAcc", fill=0.0),
               psi_form=p["lb.force.psiForm"], eqdist_form=p["lb.eqdist.eqDistForm"], enable_shan_chen=sc)
     if sc:
@@ -65,7 +67,7 @@ def lattice_kwargs(p):
     return gn, C, kw
 
 
-def initial_mask(p, blk):
+def initial_mask(p, blk, base_dir="."):
     """initMask, lb/mask.d:134-172 (one rank)."""
     kind = p["lb.mask.maskInit"]
     axis = AXIS[p["lb.mask.initAxis"]]
@@ -81,11 +83,44 @@ def initial_mask(p, blk):
         dhw = _fit(p["lb.mask.dimensionHasWall"], len(p["lattice.gn"]), "lb.mask.dimensionHasWall", fill=[False, False])
         return I.mask_walls(blk, [_fit(x, 2, "lb.mask.dimensionHasWall[i]", fill=False) for x in dhw],
                             p["lb.mask.wallThickness"])
+    if kind == "File":  # mask.d:152-154: the global mask from an HDF5 file, relative to the run directory
+        from . import h5lite
+        m = I.mask_none(blk)
+        m[blk.interior()] = h5lite.read_dataset(os.path.join(base_dir, p["lb.mask.maskFile"])).astype(m.dtype)
+        return m
     raise ReplayError(f"lb.mask.maskInit = {kind} is not supported by the replay driver")
 
 
-def initial_populations(p, blk, mask):
-    """initFluids, lb/init.d:77-136 (one rank: the rank shift of the seed is 0)."""
+def rank_grid(p, gn):
+    """The process grid the parameter file asks for (parallel.nc, parallel.d:190-237) as [(rank, M.c)], ranks in the
+    row-major order of MPI_Cart_create; a grid with a 0 (MPI_Dims_create decides) or a missing entry is one rank."""
+    nc = [int(v) for v in p.get("parallel.nc", [])]
+    if len(nc) != len(gn) or any(v < 1 for v in nc) or any(g % v for g, v in zip(gn, nc)):
+        nc = [1] * len(gn)
+    return tuple(nc), [(r, c) for r, c in enumerate(np.ndindex(*nc))]
+
+
+def _per_rank(p, blk, make):
+    """A RANDOM initialiser draws one number per site of every rank's own array (halo included), each rank from its
+    own generator (lb/init.d:109-118, random.d:43-53): emulate the ranks of parallel.nc one after the other and put
+    their blocks together.  make(rank block, rank) -> that rank's array."""
+    nc, ranks = rank_grid(p, blk.gn)
+    if len(ranks) == 1:
+        return make(blk, 0)
+    out = None
+    for r, c in ranks:
+        b = I.Block(blk.gn, halo=blk.halo, nc=nc, c=c)
+        a = make(b, r)
+        if out is None:
+            out = np.zeros(blk.shape_h + a.shape[len(blk.gn):], dtype=a.dtype)
+        dst = tuple(slice(blk.halo + ci * n, blk.halo + (ci + 1) * n) for ci, n in zip(c, b.n))
+        out[dst] = a[b.interior()]
+    return out
+
+
+def initial_populations(p, blk, mask, base_dir="."):
+    """initFluids, lb/init.d:77-136.  Deterministic initialisers are functions of the global coordinates; the random
+    ones are generated rank by rank for the process grid of the parameter file (`_per_rank`)."""
     C = int(p["lb.components"])
     form = I.EQDIST_FORMS[p["lb.eqdist.eqDistForm"]]
     kinds = _fit(p["lb.init.fluidInit"], C, "lb.init.fluidInit", fill="None")
@@ -100,27 +135,42 @@ def initial_populations(p, blk, mask):
     axis = AXIS[p["lb.init.initAxis"]]
     radius, thick = p["lb.init.initRadius"], p["lb.init.interfaceThickness"]
     widths = list(p["lb.init.lamellaeWidths"])
-    rng = Mt19937(p["random.seed"])  # the global generator (random.d:43-53), shared by the non-reseeding fluids
+    shift = bool(p.get("random.shiftSeedByRank", False))
+    nranks = len(rank_grid(p, blk.gn)[1])
+    # the global generator of every rank (random.d:43-53), shared by that rank's non-reseeding fluids
+    rngs = [Mt19937(p["random.seed"] + (r if shift else 0)) for r in range(nranks)]
     pops = []
     for f in range(C):
-        lrng = Mt19937(seeds[f]) if reseed[f] else rng
         k, d = kinds[f], list(dens[f])
+
+        def random_init(fn):
+            def make(b, r):
+                lrng = Mt19937(seeds[f] + (r if shift else 0)) if reseed[f] else rngs[r]
+                return fn(b, lrng)
+            return _per_rank(p, blk, make)
 
         def need(n):
             if len(d) != n:
                 raise ReplayError(f"Array parameter lb.init.fluidDensities[{f}] must have length {n}.")
-        if k == "Const":
+        if k == "None":  # lb/init.d:270-271: the field stays as allocated -- double.init, a quiet NaN
+            a = np.full(blk.shape_h + (conn.q,), np.nan)
+        elif k == "File":  # :272-275: the global populations from an HDF5 file, relative to the run directory
+            from . import h5lite
+            files = _fit(p["lb.init.fluidFiles"], C, "lb.init.fluidFiles", strict=True)
+            a = np.zeros(blk.shape_h + (conn.q,))
+            a[blk.interior()] = h5lite.read_dataset(os.path.join(base_dir, files[f]))
+        elif k == "Const":
             need(1); a = I.init_const(blk, conn.q, d[0])
         elif k == "ConstRandom":
-            need(1); a = I.init_const_random(blk, conn.q, d[0], lrng)
+            need(1); a = random_init(lambda b, g: I.init_const_random(b, conn.q, d[0], g))
         elif k == "EqDist":
             need(1); a = I.init_eq_dist(blk, conn, form, d[0])
         elif k == "EqDistRandom":
-            need(1); a = I.init_eq_dist_random(blk, conn, form, d[0], lrng)
+            need(1); a = random_init(lambda b, g: I.init_eq_dist_random(b, conn, form, d[0], g))
         elif k == "EqDistPerturb":
-            need(1); a = I.init_eq_dist_perturb(blk, conn, form, d[0], perturb[f], lrng)
+            need(1); a = random_init(lambda b, g: I.init_eq_dist_perturb(b, conn, form, d[0], perturb[f], g))
         elif k == "EqDistPerturbFrac":
-            need(1); a = I.init_eq_dist_perturb_frac(blk, conn, form, d[0], perturb[f], lrng)
+            need(1); a = random_init(lambda b, g: I.init_eq_dist_perturb_frac(b, conn, form, d[0], perturb[f], g))
         elif k == "EqDistSphere":
             need(2); a = I.init_eq_dist_sphere(blk, conn, form, d[0], d[1], radius, off, thick)
         elif k == "EqDistSphereFrac":
@@ -295,8 +345,8 @@ def replay(p, make_lattice=None, device_init=False, restore=None, base_dir=".", 
         blk = I.Block(gn, halo=0)
         mask, pops, device_init = mask0, pops0, False
     elif not device_init:
-        mask = initial_mask(p, blk)
-        pops = initial_populations(p, blk, mask)
+        mask = initial_mask(p, blk, base_dir)
+        pops = initial_populations(p, blk, mask, base_dir)
     L = make_lattice(gn, C, kw) if make_lattice else _cuda_lattice(gn, C, kw, **lattice_options)
     out = {}
     try:

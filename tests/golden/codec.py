@@ -27,3 +27,16 @@ def load(path):
             shape = tuple(int(x) for x in z[name + "__shape"])
             out[name] = np.ascontiguousarray(z[name].T).view(dt).reshape(shape)
     return out
+
+
+def digest(a):
+    """SHA-256 of an array's shape, dtype and bytes, with every NaN replaced by the canonical quiet NaN (a field that
+    was never initialised holds D's double.init; NaN payloads and signs are not part of what the goldens pin)."""
+    import hashlib
+    a = np.ascontiguousarray(a)
+    if a.dtype.kind == "f":
+        a = np.where(np.isnan(a), np.float64("nan"), a.astype(np.float64))
+    h = hashlib.sha256()
+    h.update(repr((a.shape, a.dtype.str)).encode())
+    h.update(np.ascontiguousarray(a).tobytes())
+    return h.hexdigest()

@@ -126,6 +126,29 @@ def main():
         for ext in (".in", ".json"):
             shutil.copy(T + f"lb/{case}/{case}{ext}", os.path.join(HERE, "in", case + ext))
 
+    # --- lb/init-2d: 32 parameter files (np = 4, nc = [2, 2]), one per fluid / mask initialiser, each with its t = 0
+    # dumps.  Kept as SHA-256 of the arrays (NaN canonicalised: FluidInit.None leaves double.init in the field) plus the
+    # three arrays the two File cases read back in; the parameter files are copied to in/init-2d/ byte for byte.
+    import hashlib
+    import json
+    import re
+    os.makedirs(os.path.join(HERE, "in", "init-2d"), exist_ok=True)
+    hashes = {}
+    for inp in sorted(glob.glob(T + "lb/init-2d/*.in")):
+        case = os.path.basename(inp)[:-3]
+        shutil.copy(inp, os.path.join(HERE, "in", "init-2d", case + ".in"))
+        hashes[case] = {}
+        for f in sorted(glob.glob(T + f"lb/init-2d/reference-data/*-{case}-t00000000.h5")):
+            stem = re.sub(r"-\d{8}T\d{6}", "", os.path.basename(f)[:-3])
+            hashes[case][stem] = codec.digest(read_dataset(f))
+    with open(os.path.join(HERE, "init-2d.json"), "w") as fh:
+        json.dump(hashes, fh, indent=1, sort_keys=True)
+    R = "lb/init-2d/reference-data/"
+    codec.save(os.path.join(HERE, "init-2d-files.npz"),
+               **{"population-red-fluid-init-file-2d-t00000000": g(R + "population-red-fluid-init-file-2d-t00000000.h5"),
+                  "population-blue-fluid-init-file-2d-t00000000": g(R + "population-blue-fluid-init-file-2d-t00000000.h5"),
+                  "mask-mask-init-file-2d-t00000000": g(R + "mask-mask-init-file-2d-t00000000.h5")})
+
     for f in sorted(glob.glob(os.path.join(HERE, "*.npz"))):
         print(f"{os.path.getsize(f):9d}  {os.path.basename(f)}")
 

@@ -403,3 +403,43 @@ def test_replay_cli_on_the_gpu(tmp_path, golden):
     R.main([os.path.join(IN, "bdist2-3d.in"), "--arith", "exact", "--out", str(tmp_path), "--run-id", "20260101T000000"])
     f = tmp_path / "density-blue-bdist2-3d-20260101T000000-t00000010.h5"
     assert_bitexact(H.read_dataset(str(f)), golden("bdist2-3d")["density-blue-t10"], "density-blue t10 (EXACT arithmetic)")
+
+
+# ---- lb/init-2d: the reference's 32 initialiser cases (every FluidInit and MaskInit, np = 4, nc = [2, 2]) ----------
+INIT2D = sorted(n[:-3] for n in os.listdir(os.path.join(IN, "init-2d")) if n.endswith(".in"))
+
+
+def _init2d_replay(case, tmp_path, golden, **options):
+    """Replay one unmodified parameter file of lb/init-2d and compare every t = 0 dump the reference holds for it
+    (populations, colour, mask) by SHA-256 (tests/golden/init-2d.json; NaN canonicalised -- FluidInit.None leaves
+    double.init in the field).  The run directory holds the files the two File cases read (fluidFiles, maskFile)."""
+    import json
+
+    import codec
+    from dlbc_b200 import h5lite as H
+    rd = tmp_path / "reference-data"
+    rd.mkdir()
+    for name, a in golden("init-2d-files").items():
+        H.write_dataset(str(rd / (name + ".h5")), a)
+    with open(os.path.join(os.path.dirname(IN), "init-2d.json")) as fh:
+        want = json.load(fh)[case]
+    p = P.parse_file(os.path.join(IN, "init-2d", case + ".in"))
+    assert p["parallel.nc"] == [2, 2] and p["lb.timesteps"] == 0
+    out = R.replay(p, base_dir=str(tmp_path), **options)
+    assert len(want) == 4
+    for stem, digest in want.items():
+        assert codec.digest(out[stem]) == digest, f"{case}: {stem} differs from the reference's file"
+
+
+@pytest.mark.parametrize("case", INIT2D)
+def test_init_2d_cases_on_the_oracle(case, tmp_path, golden):
+    """host initialisers (init.py) incl. the per-rank random streams of a 2 x 2 process grid, FluidInit None / File,
+    MaskInit File, and the t = 0 outputs, through the oracle's D2Q9 lattice."""
+    _init2d_replay(case, tmp_path, golden, make_lattice=_oracle_lattice)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", INIT2D)
+def test_init_2d_cases_on_the_gpu(case, tmp_path, golden):
+    """the same through a 2-D context of libdlbc_cuda (upload, colour / mask / population downloads of csrc/d2q9.cu)."""
+    _init2d_replay(case, tmp_path, golden, arithmetic="exact")
