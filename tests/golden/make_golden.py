@@ -11,6 +11,7 @@ files are DLBC's own regression data, tests/runnable/tests/**/reference-data/*.h
 """
 import glob
 import os
+import shutil
 import sys
 
 import numpy as np
@@ -125,6 +126,21 @@ def main():
         codec.save(os.path.join(HERE, case + ".npz"), **out)
         for ext in (".in", ".json"):
             shutil.copy(T + f"lb/{case}/{case}{ext}", os.path.join(HERE, "in", case + ext))
+
+    # --- technical/checkpoint-2d (d2q9): input file an .h5 (extracted to in/checkpoint-2d.in), restart from cp files, t = 0, 10
+    C2 = "technical/checkpoint-2d/"
+    tid = "20150321T122217"
+    lines2 = _h5.read_attributes(T + C2 + f"reference-data/colour-red-blue-checkpoint-2d-{tid}-t00000000.h5")["input"]
+    with open(os.path.join(HERE, "in", "checkpoint-2d.in"), "w") as _f:
+        _f.write("\n".join(lines2) + "\n")
+    shutil.copy(T + C2 + "checkpoint-2d.json", os.path.join(HERE, "in", "checkpoint-2d.json"))
+    out = {}
+    for name in ("cp-fluids0", "cp-fluids1", "cp-mask"):
+        out[f"{name}-t0"] = g(C2 + f"reference-data/cp/{name}-checkpoint-2d-{tid}-t00000000.h5")
+    for t in (0, 10):
+        for d in ("colour-red-blue", "density-red", "density-blue", "population-red", "population-blue"):
+            out[f"{d}-t{t}"] = g(C2 + f"reference-data/{d}-checkpoint-2d-{tid}-t{t:08d}.h5")
+    codec.save(os.path.join(HERE, "checkpoint-2d.npz"), **out)
 
     # --- lb/init-2d: 32 parameter files (np = 4, nc = [2, 2]), one per fluid / mask initialiser, each with its t = 0
     # dumps.  Kept as SHA-256 of the arrays (NaN canonicalised: FluidInit.None leaves double.init in the field) plus the

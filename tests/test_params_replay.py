@@ -203,6 +203,40 @@ def _checkpoint_test_dir(tmp_path, g):
     return str(tmp_path / "checkpoint-3d.json")
 
 
+def _checkpoint_2d(golden, tmp_path, **options):
+    """technical/checkpoint-2d (d2q9): the same flow in 2-D -- the spec's input file and checkpoint name carry the run id
+    of the reference's files; the directory is rebuilt from the fixtures with this repo's HDF5 writer."""
+    import shutil
+    from dlbc_b200 import h5lite as H
+    from dlbc_b200.testspec import TestSpec
+    g, tid = golden("checkpoint-2d"), "20150321T122217"
+    lines = P.read_lines(os.path.join(IN, "checkpoint-2d.in"))
+    rd = tmp_path / "reference-data"
+    (rd / "cp").mkdir(parents=True)
+    # (the spec names its input file relative to the test directory; the reference keeps a copy of it there)
+    for d in (tmp_path, rd):
+        H.write_file(str(d / f"colour-red-blue-checkpoint-2d-{tid}-t00000000.h5"), g["colour-red-blue-t0"], input_lines=lines,
+                     metadata=R.metadata())
+    for name in ("cp-fluids0", "cp-fluids1", "cp-mask"):
+        H.write_file(str(rd / "cp" / f"{name}-checkpoint-2d-{tid}-t00000000.h5"), g[f"{name}-t0"], input_lines=lines,
+                     metadata=R.metadata(), globals_={"dlbc.lb.lb.timestep": 0})
+    shutil.copy(os.path.join(IN, "checkpoint-2d.json"), tmp_path / "checkpoint-2d.json")
+    spec = TestSpec(str(tmp_path / "checkpoint-2d.json"))
+    assert spec.configuration == "d2q9" and spec.checkpoint == {"name": f"checkpoint-2d-{tid}-t00000000"}
+    rep = spec.run(g, "full", floor=1e-15, **options)
+    assert {t for _, t, _, _ in rep} == {0, 10} and all(d == 0.0 for _, t, d, _ in rep if t == 0)
+    assert len(rep) == 10
+
+
+def test_checkpoint_2d_spec_on_the_oracle(golden, tmp_path):
+    _checkpoint_2d(golden, tmp_path, make_lattice=_oracle_lattice)
+
+
+@pytest.mark.gpu
+def test_checkpoint_2d_spec_on_the_gpu(golden, tmp_path):
+    _checkpoint_2d(golden, tmp_path, arithmetic="exact")
+
+
 def test_h5_attributes_roundtrip(tmp_path):
     from dlbc_b200 import h5lite as H
     lines = P.read_lines(os.path.join(IN, "checkpoint-3d.in"))
