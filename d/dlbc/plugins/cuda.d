@@ -132,14 +132,21 @@ private void check(int e, string what) {
    Requires the z-slab decomposition the library implements: `parallel.nc = [1, 1, M.size]`.
 */
 void uploadLattice(T)(ref T L) if ( isLattice!T ) {
-  static assert(T.lbconn.d == 3 && T.lbconn.q == 19, "libdlbc_cuda implements D3Q19 only.");
-  if ( M.nc[0] != 1 || M.nc[1] != 1 ) {
-    writeLogF("cuda.enable requires parallel.nc = [1, 1, %d] (z-slabs).", M.size);
+  alias conn = T.lbconn;
+  static assert((conn.d == 3 && conn.q == 19) || (conn.d == 2 && conn.q == 9),
+                "libdlbc_cuda implements D3Q19 and D2Q9 (a version(D2Q9) build: one rank).");
+  static if ( conn.d == 3 ) {
+    if ( M.nc[0] != 1 || M.nc[1] != 1 ) {
+      writeLogF("cuda.enable requires parallel.nc = [1, 1, %d] (z-slabs).", M.size);
+    }
+  }
+  else {
+    if ( M.size != 1 ) writeLogF("cuda.enable on a 2-D lattice runs on one rank.");
   }
   dlbc_cuda_config cfg;
   cfg.abi_version = DLBC_CUDA_ABI_VERSION;
-  cfg.d = 3; cfg.q = 19;
-  foreach(immutable i; 0..3) cfg.gn[i] = L.gn[i];
+  cfg.d = conn.d; cfg.q = conn.q;
+  foreach(immutable i; 0..conn.d) cfg.gn[i] = L.gn[i];
   cfg.ncomp = cast(int) L.fluids.length;
   foreach(immutable f; 0..L.fluids.length) {
     cfg.tau[f] = tau[f];
@@ -148,21 +155,27 @@ void uploadLattice(T)(ref T L) if ( isLattice!T ) {
       cfg.gcc[f * DLBC_CUDA_MAX_COMPONENTS + f2] = enableShanChen ? gcc[f][f2] : 0.0;
     }
   }
-  foreach(immutable i; 0..3) cfg.global_acc[i] = globalAcc[i];
+  foreach(immutable i; 0..conn.d) cfg.global_acc[i] = globalAcc[i];
   cfg.psi_form = cast(int) psiForm;        // enum order = DLBC_PSI_*   (lb/force.d:48-57)
   cfg.eqdist_form = cast(int) eqDistForm;  // enum order = DLBC_EQDIST_* (lb/eqdist.d:23-36)
   cfg.enable_shan_chen = enableShanChen ? 1 : 0;
   cfg.arithmetic = arithmetic;
   cfg.kernel_variant = kernelVariant;
   cfg.device = deviceOffset + M.rank % devicesPerNode;
-  cfg.rank = M.c[2];
-  cfg.nranks = M.nc[2];
+  static if ( conn.d == 3 ) {
+    cfg.rank = M.c[2];
+    cfg.nranks = M.nc[2];
+  }
+  else {
+    cfg.rank = 0;
+    cfg.nranks = 1;
+  }
   if ( M.size > 1 ) {
     if ( M.isRoot ) check(dlbc_cuda_nccl_unique_id(cfg.nccl_id.ptr), "dlbc_cuda_nccl_unique_id");
     MPI_Bcast(cfg.nccl_id.ptr, DLBC_CUDA_NCCL_ID_BYTES, MPI_BYTE, M.root, M.comm);
   }
   check(dlbc_cuda_create(&cfg, &ctx), "dlbc_cuda_create");
-  // Field.arr._data.ptr is the [nx+4][ny+4][nz+4]([19]) block the library expects with halo = 2.
+  // Field.arr._data.ptr is the [nx+4][ny+4][nz+4]([19]) block ([nx+4][ny+4]([9]) in 2-D) the library expects with halo = 2.
   check(dlbc_cuda_upload_mask(ctx, cast(const(int)*) L.mask.arr._data.ptr, 2), "dlbc_cuda_upload_mask");
   foreach(immutable f, ref field; L.fluids) {
     check(dlbc_cuda_upload_populations(ctx, cast(int) f, cast(const(double)*) field.arr._data.ptr, 2),
