@@ -113,11 +113,12 @@ def main():
     # --- the 2-D (D2Q9) spec cases: what their fast runs compare (t = 0 and the fast run's last dump), whole arrays;
     # the parameter files and JSON specs are copied to in/ byte for byte
     import shutil
+    # (+ the last dump of the FULL runs of the two Shan-Chen cases: t = 100 and t = 1000)
     for case, times, data in (("bdist2-2d", (0, 10), ("density-red", "density-blue", "population-red", "population-blue")),
-                              ("bdist2-sc-2d", (0, 10), ("colour-red-blue", "density-red", "density-blue", "population-red",
-                                                         "population-blue")),
-                              ("merging-droplets-2d", (0, 100), ("colour-red-blue", "density-red", "density-blue",
-                                                                 "population-red", "population-blue")),
+                              ("bdist2-sc-2d", (0, 10, 100), ("colour-red-blue", "density-red", "density-blue", "population-red",
+                                                              "population-blue")),
+                              ("merging-droplets-2d", (0, 100, 1000), ("colour-red-blue", "density-red", "density-blue",
+                                                                       "population-red", "population-blue")),
                               ("laplace-droplet-2d", (0, 100), ("colour-red-blue", "density-red", "density-blue"))):
         out = {}
         for t in times:

@@ -169,6 +169,15 @@ def test_spec_driven_replay_on_the_oracle(golden, case):
     assert any(t >= 10 for _, t, _, _ in rep) and all(d == 0.0 for _, t, d, _ in rep if t == 0)
 
 
+@pytest.mark.parametrize("case,last", [("bdist2-sc-2d", 100), ("merging-droplets-2d", 1000)])
+def test_full_runs_of_the_2d_shan_chen_specs_on_the_oracle(golden, case, last):
+    """the specs' FULL mode (no overrides): the last dump of the whole run within the spec's own accuracy (1e-14)."""
+    from dlbc_b200.testspec import TestSpec
+    rep = TestSpec(os.path.join(IN, case + ".json")).run(golden(case), "full", make_lattice=_oracle_lattice)
+    assert {t for _, t, _, _ in rep} == {0, last} and all(a == 1e-14 for _, t, _, a in rep if t == last)
+    assert all(d == 0.0 for _, t, d, _ in rep if t == 0)
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("case", SPECS)
 def test_spec_driven_replay_on_the_gpu(golden, case):
