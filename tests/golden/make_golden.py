@@ -102,6 +102,8 @@ def main():
             for f in ("density", "velocity", "force"):
                 out[f"{f}-{c}-t{t}"] = g(f"lb/poiseuille-2d/reference-data/{f}-{c}-*t{t:08d}.h5")
     codec.save(os.path.join(HERE, "poiseuille-2d.npz"), **out)
+    for ext in (".in", ".json"):
+        shutil.copy(T + "lb/poiseuille-2d/poiseuille-2d" + ext, os.path.join(HERE, "in", "poiseuille-2d" + ext))
 
     # --- lb/init-2d: the random initialisers (np = 4, nc = [2, 2]) pin Mt19937 + uniform
     out = {}

@@ -169,6 +169,17 @@ def test_spec_driven_replay_on_the_oracle(golden, case):
     assert any(t >= 10 for _, t, _, _ in rep) and all(d == 0.0 for _, t, d, _ in rep if t == 0)
 
 
+def test_poiseuille_2d_spec_on_the_oracle(golden):
+    """lb/poiseuille-2d from its unmodified parameter file: plates, bounce-back, body force; mask / density / velocity /
+    force dumps at t = 0 (exact) and t = 1000.  The spec's fast run grants no accuracy at t = 1000; gcc's arithmetic
+    is within 5e-15 of the DMD-written goldens there (tests/test_oracle_golden.py pins the same number)."""
+    from dlbc_b200.testspec import TestSpec
+    rep = TestSpec(os.path.join(IN, "poiseuille-2d.json")).run(golden("poiseuille-2d"), "fast", make_lattice=_oracle_lattice,
+                                                               floor=5e-15)
+    assert {t for _, t, _, _ in rep} == {0, 1000} and len(rep) == 14 and all(d == 0.0 for _, t, d, _ in rep if t == 0)
+    assert all(d == 0.0 for name, _, d, _ in rep if name == "mask" or name.startswith("force"))
+
+
 @pytest.mark.parametrize("case,last", [("bdist2-sc-2d", 100), ("merging-droplets-2d", 1000)])
 def test_full_runs_of_the_2d_shan_chen_specs_on_the_oracle(golden, case, last):
     """the specs' FULL mode (no overrides): the last dump of the whole run within the spec's own accuracy (1e-14)."""
